@@ -1,0 +1,291 @@
+// Fused element-wise kernels for sm_100a (SURVEY §8 G7 backward, A1 RoPE, D1, E1).
+//
+//  * SwiGLU forward/backward on the (gate | up) pre-activation layout produced by the dual-GEMM epilogue
+//    (reference: silu(dense_in(x)) * siglu_weight(x), core/nn/mlp.py:157-160 — 2 ATen kernels fwd, ≈6 bwd).
+//  * Rotary embedding, both flavours, in place on packed q/k (reference: core/nn/rotary.py:68-139, 6–10 ATen kernels);
+//    the backward pass is the same kernel with the rotation direction flipped.
+//  * bias + dropout + residual (reference: tfm/model/layers/layer.py:211-216) with a counter-based Philox stream, so
+//    the mask is identical on every tensor-parallel rank and under activation recomputation without RNG state forking.
+//  * Vocab-parallel embedding gather (masked) and its scatter-add backward into the main-grad buffer
+//    (reference: core/nn/linear/vocab_parallel_embedding.py:119-147).
+#include "common.cuh"
+
+namespace sb {
+namespace ew {
+
+// ------------------------------------------------------------------ SwiGLU
+// pre: [rows, 2F] (gate cols [0,F), up cols [F,2F)), h: [rows, F]
+__global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ pre, __nv_bfloat16* __restrict__ h, int rows, int F) {
+  const size_t n8 = (size_t)rows * F / 8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t e = i * 8;
+    const size_t r = e / F, c = e % F;
+    uint4 g = *reinterpret_cast<const uint4*>(pre + r * 2 * F + c);
+    uint4 u = *reinterpret_cast<const uint4*>(pre + r * 2 * F + F + c);
+    const uint32_t* gp = &g.x;
+    const uint32_t* up = &u.x;
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 a = unpack_bf16(gp[j]), b = unpack_bf16(up[j]);
+      o[j] = pack_bf16(silu_f(a.x) * b.x, silu_f(a.y) * b.y);
+    }
+    *reinterpret_cast<uint4*>(h + e) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// dpre = [dh * u * silu'(g) | dh * silu(g)]; optionally recomputes h (needed by the down-projection wgrad when the
+// forward did not keep it)
+__global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ pre, const __nv_bfloat16* __restrict__ dh,
+                                  __nv_bfloat16* __restrict__ dpre, __nv_bfloat16* __restrict__ h_out, int rows, int F) {
+  const size_t n8 = (size_t)rows * F / 8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t e = i * 8;
+    const size_t r = e / F, c = e % F;
+    uint4 g = *reinterpret_cast<const uint4*>(pre + r * 2 * F + c);
+    uint4 u = *reinterpret_cast<const uint4*>(pre + r * 2 * F + F + c);
+    uint4 d = *reinterpret_cast<const uint4*>(dh + e);
+    const uint32_t *gp = &g.x, *up = &u.x, *dp = &d.x;
+    uint32_t og[4], ou[4], oh[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 a = unpack_bf16(gp[j]), b = unpack_bf16(up[j]), dd = unpack_bf16(dp[j]);
+      float s0 = 1.f / (1.f + __expf(-a.x)), s1 = 1.f / (1.f + __expf(-a.y));
+      float act0 = a.x * s0, act1 = a.y * s1;
+      float dact0 = s0 * (1.f + a.x * (1.f - s0)), dact1 = s1 * (1.f + a.y * (1.f - s1));
+      og[j] = pack_bf16(dd.x * b.x * dact0, dd.y * b.y * dact1);
+      ou[j] = pack_bf16(dd.x * act0, dd.y * act1);
+      oh[j] = pack_bf16(act0 * b.x, act1 * b.y);
+    }
+    *reinterpret_cast<uint4*>(dpre + r * 2 * F + c) = make_uint4(og[0], og[1], og[2], og[3]);
+    *reinterpret_cast<uint4*>(dpre + r * 2 * F + F + c) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+    if (h_out) *reinterpret_cast<uint4*>(h_out + e) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+  }
+}
+
+// ------------------------------------------------------------------ activation (gelu / silu) fwd+bwd, bf16
+template <int kAct>
+__global__ void act_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, size_t n) {
+  for (size_t i = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 2; i < n; i += (size_t)gridDim.x * blockDim.x * 2) {
+    float2 v = unpack_bf16(*reinterpret_cast<const uint32_t*>(x + i));
+    float a = kAct ? silu_f(v.x) : gelu_f(v.x), b = kAct ? silu_f(v.y) : gelu_f(v.y);
+    *reinterpret_cast<uint32_t*>(y + i) = pack_bf16(a, b);
+  }
+}
+SB_DEVICE float dgelu(float x) {
+  const float k = 0.70710678118654752f;
+  return 0.5f * (1.f + erff(x * k)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+SB_DEVICE float dsilu(float x) {
+  float s = 1.f / (1.f + __expf(-x));
+  return s * (1.f + x * (1.f - s));
+}
+template <int kAct>
+__global__ void act_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                               __nv_bfloat16* __restrict__ dx, size_t n) {
+  for (size_t i = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 2; i < n; i += (size_t)gridDim.x * blockDim.x * 2) {
+    float2 v = unpack_bf16(*reinterpret_cast<const uint32_t*>(x + i));
+    float2 d = unpack_bf16(*reinterpret_cast<const uint32_t*>(dy + i));
+    float a = kAct ? dsilu(v.x) : dgelu(v.x), b = kAct ? dsilu(v.y) : dgelu(v.y);
+    *reinterpret_cast<uint32_t*>(dx + i) = pack_bf16(a * d.x, b * d.y);
+  }
+}
+
+// ------------------------------------------------------------------ rotary
+// x: [tokens, heads, head_dim] bf16 with token stride `ts` elements; cos/sin: fp32 [max_pos, rot_dim/2];
+// pos: int32 [tokens] (may be null -> token index modulo seq).  mode 0: interleaved pairs (rotary_complex),
+// mode 1: half rotation (NeoX "rotary"). dir = +1 forward, -1 backward (inverse rotation).
+__global__ void rope_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ cs, const float* __restrict__ sn,
+                            const int* __restrict__ pos, int tokens, int heads, int head_dim, int rot_dim, long long ts,
+                            int seq, int mode, float dir) {
+  const int half = rot_dim / 2;
+  const size_t total = (size_t)tokens * heads * half;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int j = i % half;
+    const size_t th = i / half;
+    const int hd = th % heads;
+    const int t = th / heads;
+    const int p = pos ? pos[t] : (t % seq);
+    const float c = cs[(size_t)p * half + j], s = dir * sn[(size_t)p * half + j];
+    __nv_bfloat16* base = x + (size_t)t * ts + (size_t)hd * head_dim;
+    const int i0 = mode == 0 ? 2 * j : j, i1 = mode == 0 ? 2 * j + 1 : j + half;
+    const float a = __bfloat162float(base[i0]), b = __bfloat162float(base[i1]);
+    base[i0] = __float2bfloat16(a * c - b * s);
+    base[i1] = __float2bfloat16(a * s + b * c);
+  }
+}
+
+// ------------------------------------------------------------------ bias + dropout + residual
+// out = residual + dropout(x + bias); mask derived from Philox(seed, element index) — nothing is stored
+__global__ void bias_dropout_add_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ bias,
+                                        const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ out,
+                                        size_t n, int cols, float p, unsigned long long seed,
+                                        unsigned long long offset) {
+  const float scale = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  Philox rng(seed);
+  for (size_t i = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 4; i < n; i += (size_t)gridDim.x * blockDim.x * 4) {
+    uint2 xv = *reinterpret_cast<const uint2*>(x + i);
+    float2 a = unpack_bf16(xv.x), b = unpack_bf16(xv.y);
+    float v[4] = {a.x, a.y, b.x, b.y};
+    if (bias) {
+      const int c = i % cols;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] += __bfloat162float(bias[c + k]);
+    }
+    if (p > 0.f) {
+      uint4 r = rng(i / 4, offset);
+      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = (rr[k] * 2.3283064365386963e-10f >= p) ? v[k] * scale : 0.f;
+    }
+    if (residual) {
+      uint2 rv = *reinterpret_cast<const uint2*>(residual + i);
+      float2 c0 = unpack_bf16(rv.x), c1 = unpack_bf16(rv.y);
+      v[0] += c0.x, v[1] += c0.y, v[2] += c1.x, v[3] += c1.y;
+    }
+    *reinterpret_cast<uint2*>(out + i) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+  }
+}
+// dx = dout * mask * scale  (the residual branch gradient is dout itself)
+__global__ void dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ dx, size_t n,
+                                   float p, unsigned long long seed, unsigned long long offset) {
+  const float scale = 1.f / (1.f - p);
+  Philox rng(seed);
+  for (size_t i = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 4; i < n; i += (size_t)gridDim.x * blockDim.x * 4) {
+    uint2 dv = *reinterpret_cast<const uint2*>(dout + i);
+    float2 a = unpack_bf16(dv.x), b = unpack_bf16(dv.y);
+    float v[4] = {a.x, a.y, b.x, b.y};
+    uint4 r = rng(i / 4, offset);
+    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = (rr[k] * 2.3283064365386963e-10f >= p) ? v[k] * scale : 0.f;
+    *reinterpret_cast<uint2*>(dx + i) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+  }
+}
+
+// ------------------------------------------------------------------ vocab-parallel embedding
+// out[t] = (vocab_start <= id < vocab_end) ? W[id - vocab_start] : 0
+__global__ void embedding_fwd_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ W,
+                                     __nv_bfloat16* __restrict__ out, int tokens, int hidden, long long vocab_start,
+                                     long long vocab_end) {
+  const int per_row = hidden / 8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < (size_t)tokens * per_row;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int t = i / per_row, c = (i % per_row) * 8;
+    const long long id = ids[t];
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (id >= vocab_start && id < vocab_end) v = *reinterpret_cast<const uint4*>(W + (size_t)(id - vocab_start) * hidden + c);
+    *reinterpret_cast<uint4*>(out + (size_t)t * hidden + c) = v;
+  }
+}
+template <typename G>
+__global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ dout,
+                                     G* __restrict__ dW, int tokens, int hidden, long long vocab_start,
+                                     long long vocab_end) {
+  const int per_row = hidden / 2;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < (size_t)tokens * per_row;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int t = i / per_row, c = (i % per_row) * 2;
+    const long long id = ids[t];
+    if (id < vocab_start || id >= vocab_end) continue;
+    float2 d = unpack_bf16(*reinterpret_cast<const uint32_t*>(dout + (size_t)t * hidden + c));
+    G* dst = dW + (size_t)(id - vocab_start) * hidden + c;
+    if constexpr (sizeof(G) == 4) {
+      atomicAdd(reinterpret_cast<float*>(dst), d.x);
+      atomicAdd(reinterpret_cast<float*>(dst) + 1, d.y);
+    } else {
+      atomicAdd(reinterpret_cast<__nv_bfloat162*>(dst), __floats2bfloat162_rn(d.x, d.y));
+    }
+  }
+}
+
+static int blocks_for(size_t work, int threads = 256) {
+  size_t b = (work + threads - 1) / threads;
+  size_t cap = 148 * 16;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace ew
+}  // namespace sb
+
+using namespace sb::ew;
+
+extern "C" int sb_swiglu_fwd(const void* pre, void* h, int rows, int F, cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (F % 8) return -1;
+  swiglu_fwd_kernel<<<blocks_for((size_t)rows * F / 8), 256, 0, st>>>((const __nv_bfloat16*)pre, (__nv_bfloat16*)h, rows, F);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_swiglu_bwd(const void* pre, const void* dh, void* dpre, void* h_out, int rows, int F,
+                             cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (F % 8) return -1;
+  swiglu_bwd_kernel<<<blocks_for((size_t)rows * F / 8), 256, 0, st>>>(
+      (const __nv_bfloat16*)pre, (const __nv_bfloat16*)dh, (__nv_bfloat16*)dpre, (__nv_bfloat16*)h_out, rows, F);
+  return (int)cudaGetLastError();
+}
+// act: 0 gelu, 1 silu
+extern "C" int sb_act_fwd(const void* x, void* y, long long n, int act, cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n % 2) return -1;
+  if (act)
+    act_fwd_kernel<1><<<blocks_for(n / 2), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
+  else
+    act_fwd_kernel<0><<<blocks_for(n / 2), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_act_bwd(const void* x, const void* dy, void* dx, long long n, int act, cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n % 2) return -1;
+  if (act)
+    act_bwd_kernel<1><<<blocks_for(n / 2), 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n);
+  else
+    act_bwd_kernel<0><<<blocks_for(n / 2), 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_rope(void* x, const float* cos_t, const float* sin_t, const int* pos, int tokens, int heads,
+                       int head_dim, int rot_dim, long long token_stride, int seq, int mode, int backward,
+                       cudaStream_t st) {
+  if (tokens <= 0 || rot_dim <= 0) return 0;
+  rope_kernel<<<blocks_for((size_t)tokens * heads * (rot_dim / 2)), 256, 0, st>>>(
+      (__nv_bfloat16*)x, cos_t, sin_t, pos, tokens, heads, head_dim, rot_dim, token_stride, seq, mode,
+      backward ? -1.f : 1.f);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_bias_dropout_add(const void* x, const void* bias, const void* residual, void* out, long long n,
+                                   int cols, float p, unsigned long long seed, unsigned long long offset,
+                                   cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n % 4 || cols % 4) return -1;
+  bias_dropout_add_kernel<<<blocks_for(n / 4), 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)bias,
+                                                            (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, n, cols,
+                                                            p, seed, offset);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_dropout_bwd(const void* dout, void* dx, long long n, float p, unsigned long long seed,
+                              unsigned long long offset, cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n % 4) return -1;
+  dropout_bwd_kernel<<<blocks_for(n / 4), 256, 0, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)dx, n, p, seed, offset);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_embedding_fwd(const long long* ids, const void* W, void* out, int tokens, int hidden,
+                                long long vocab_start, long long vocab_end, cudaStream_t st) {
+  if (tokens <= 0) return 0;
+  if (hidden % 8) return -1;
+  embedding_fwd_kernel<<<blocks_for((size_t)tokens * hidden / 8), 256, 0, st>>>(ids, (const __nv_bfloat16*)W,
+                                                                              (__nv_bfloat16*)out, tokens, hidden,
+                                                                              vocab_start, vocab_end);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_embedding_bwd(const long long* ids, const void* dout, void* dW, int grad_fp32, int tokens, int hidden,
+                                long long vocab_start, long long vocab_end, cudaStream_t st) {
+  if (tokens <= 0) return 0;
+  if (hidden % 2) return -1;
+  const int b = blocks_for((size_t)tokens * hidden / 2);
+  if (grad_fp32)
+    embedding_bwd_kernel<float><<<b, 256, 0, st>>>(ids, (const __nv_bfloat16*)dout, (float*)dW, tokens, hidden, vocab_start, vocab_end);
+  else
+    embedding_bwd_kernel<__nv_bfloat16><<<b, 256, 0, st>>>(ids, (const __nv_bfloat16*)dout, (__nv_bfloat16*)dW, tokens, hidden, vocab_start, vocab_end);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,299 @@
+// RMSNorm / LayerNorm forward + backward for sm_100a.
+//
+// Replaces the reference's RMSNorm (≈6 ATen kernels with an fp32 round trip, core/nn/norm/rms_norm.py:45-53) and
+// F.layer_norm (core/nn/norm/layernorm.py:72-79) with single-pass kernels: bf16/fp32 I/O, fp32 statistics, 128-bit
+// loads, optional fused residual add (h = x + r is written once and normalised in the same pass), and a weight/bias
+// gradient that is accumulated per CTA in shared memory, spilled to a [grid, cols] fp32 scratch and column-reduced
+// straight into the (fp32 or bf16) main-grad buffer.
+#include "common.cuh"
+
+namespace sb {
+namespace norm {
+
+constexpr int kThreads = 256;
+
+template <typename T>
+struct Vec8;
+template <>
+struct Vec8<__nv_bfloat16> {
+  static SB_DEVICE void load(const __nv_bfloat16* p, float* f) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    float2 a = unpack_bf16(v.x), b = unpack_bf16(v.y), c = unpack_bf16(v.z), d = unpack_bf16(v.w);
+    f[0] = a.x, f[1] = a.y, f[2] = b.x, f[3] = b.y, f[4] = c.x, f[5] = c.y, f[6] = d.x, f[7] = d.y;
+  }
+  static SB_DEVICE void store(__nv_bfloat16* p, const float* f) {
+    *reinterpret_cast<uint4*>(p) =
+        make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  }
+  static SB_DEVICE float round(float x) { return __bfloat162float(__float2bfloat16(x)); }
+};
+template <>
+struct Vec8<float> {
+  static SB_DEVICE void load(const float* p, float* f) {
+    float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+    f[0] = a.x, f[1] = a.y, f[2] = a.z, f[3] = a.w, f[4] = b.x, f[5] = b.y, f[6] = b.z, f[7] = b.w;
+  }
+  static SB_DEVICE void store(float* p, const float* f) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+  }
+  static SB_DEVICE float round(float x) { return x; }
+};
+template <>
+struct Vec8<__half> {
+  static SB_DEVICE void load(const __half* p, float* f) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 t = __half22float2(h[i]);
+      f[2 * i] = t.x, f[2 * i + 1] = t.y;
+    }
+  }
+  static SB_DEVICE void store(__half* p, const float* f) {
+    uint4 v;
+    __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = v;
+  }
+  static SB_DEVICE float round(float x) { return __half2float(__float2half(x)); }
+};
+
+SB_DEVICE float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
+  if (w == 0) {
+    t = warp_sum(t);
+    if (l == 0) red[0] = t;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+// y = norm(x [+ res]) * w (+ b);  kRms: no mean subtraction, no bias.  sum_out (optional) receives x + res.
+template <typename T, bool kRms>
+__global__ void __launch_bounds__(kThreads) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                            const T* __restrict__ w, const T* __restrict__ b,
+                                                            T* __restrict__ y, T* __restrict__ sum_out,
+                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                            int rows, int cols, float eps) {
+  __shared__ float red[32];
+  extern __shared__ float row_cache[];  // cols floats
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const T* xr = x + (size_t)r * cols;
+    float s = 0.f, ss = 0.f;
+    for (int c = threadIdx.x * 8; c < cols; c += kThreads * 8) {
+      float f[8];
+      Vec8<T>::load(xr + c, f);
+      if (res) {
+        float g[8];
+        Vec8<T>::load(res + (size_t)r * cols + c, g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = Vec8<T>::round(f[i] + g[i]);
+        if (sum_out) Vec8<T>::store(sum_out + (size_t)r * cols + c, f);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        row_cache[c + i] = f[i];
+        s += f[i];
+        ss += f[i] * f[i];
+      }
+    }
+    float mean = 0.f, rstd;
+    if (kRms) {
+      ss = block_sum(ss, red);
+      rstd = rsqrtf(ss / cols + eps);
+    } else {
+      s = block_sum(s, red);
+      mean = s / cols;
+      float var = 0.f;
+      for (int c = threadIdx.x * 8; c < cols; c += kThreads * 8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float d = row_cache[c + i] - mean;
+          var += d * d;
+        }
+      }
+      var = block_sum(var, red);
+      rstd = rsqrtf(var / cols + eps);
+    }
+    if (threadIdx.x == 0) {
+      if (mean_out) mean_out[r] = mean;
+      rstd_out[r] = rstd;
+    }
+    T* yr = y + (size_t)r * cols;
+    for (int c = threadIdx.x * 8; c < cols; c += kThreads * 8) {
+      float wv[8], o[8];
+      Vec8<T>::load(w + c, wv);
+      if (kRms) {
+        // reference order: normalise in fp32, cast to the model dtype, then scale by the weight
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = Vec8<T>::round(row_cache[c + i] * rstd) * wv[i];
+      } else {
+        float bv[8];
+        if (b) Vec8<T>::load(b + c, bv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = (row_cache[c + i] - mean) * rstd * wv[i] + (b ? bv[i] : 0.f);
+      }
+      Vec8<T>::store(yr + c, o);
+    }
+    __syncthreads();
+  }
+}
+
+// dx (+= dres) and per-CTA partial dw/db. x is the normalised layer's input (after the residual add).
+template <typename T, bool kRms>
+__global__ void __launch_bounds__(kThreads) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                            const T* __restrict__ w, const float* __restrict__ mean_in,
+                                                            const float* __restrict__ rstd_in,
+                                                            const T* __restrict__ dres, T* __restrict__ dx,
+                                                            float* __restrict__ partial_dw, float* __restrict__ partial_db,
+                                                            int rows, int cols) {
+  __shared__ float red[32];
+  extern __shared__ float sm[];  // [cols] dw accumulators, [cols] db accumulators (LayerNorm only)
+  float* acc_w = sm;
+  float* acc_b = sm + cols;
+  for (int c = threadIdx.x; c < cols; c += kThreads) {
+    acc_w[c] = 0.f;
+    if (!kRms) acc_b[c] = 0.f;
+  }
+  __syncthreads();
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const T* xr = x + (size_t)r * cols;
+    const T* dyr = dy + (size_t)r * cols;
+    const float rstd = rstd_in[r];
+    const float mean = kRms ? 0.f : mean_in[r];
+    float s1 = 0.f, s2 = 0.f;  // Σ g·xhat, Σ g  with g = dy·w
+    for (int c = threadIdx.x * 8; c < cols; c += kThreads * 8) {
+      float xv[8], dv[8], wv[8];
+      Vec8<T>::load(xr + c, xv);
+      Vec8<T>::load(dyr + c, dv);
+      Vec8<T>::load(w + c, wv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float xhat = (xv[i] - mean) * rstd;
+        float g = dv[i] * wv[i];
+        s1 += g * xhat;
+        s2 += g;
+        acc_w[c + i] += dv[i] * (kRms ? Vec8<T>::round(xhat) : xhat);
+        if (!kRms) acc_b[c + i] += dv[i];
+      }
+    }
+    s1 = block_sum(s1, red) / cols;
+    if (!kRms) s2 = block_sum(s2, red) / cols;
+    T* dxr = dx + (size_t)r * cols;
+    for (int c = threadIdx.x * 8; c < cols; c += kThreads * 8) {
+      float xv[8], dv[8], wv[8], o[8];
+      Vec8<T>::load(xr + c, xv);
+      Vec8<T>::load(dyr + c, dv);
+      Vec8<T>::load(w + c, wv);
+      float rv[8];
+      if (dres) Vec8<T>::load(dres + (size_t)r * cols + c, rv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float xhat = (xv[i] - mean) * rstd;
+        float g = dv[i] * wv[i];
+        o[i] = rstd * (g - xhat * s1 - (kRms ? 0.f : s2));
+        if (dres) o[i] += rv[i];
+      }
+      Vec8<T>::store(dxr + c, o);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += kThreads) {
+    partial_dw[(size_t)blockIdx.x * cols + c] = acc_w[c];
+    if (!kRms) partial_db[(size_t)blockIdx.x * cols + c] = acc_b[c];
+  }
+}
+
+// column-reduce the per-CTA partials; accumulate==1 adds to the existing gradient (main-grad semantics)
+template <typename G>
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, G* __restrict__ grad, int parts, int cols,
+                                       int accumulate) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int p = 0; p < parts; ++p) s += partial[(size_t)p * cols + c];
+  if (accumulate) s += (float)grad[c];
+  grad[c] = (G)s;
+}
+
+static int grid_for(int rows) {
+  int n = 148 * 4;
+  return rows < n ? rows : n;
+}
+
+template <typename T>
+static int fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
+               float* rstd, int rows, int cols, float eps, int rms, cudaStream_t st) {
+  if (cols % 8) return -1;
+  size_t smem = (size_t)cols * 4;
+  auto k = rms ? norm_fwd_kernel<T, true> : norm_fwd_kernel<T, false>;
+  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k<<<rows, kThreads, smem, st>>>((const T*)x, (const T*)res, (const T*)w, (const T*)b, (T*)y, (T*)sum_out, mean, rstd,
+                                 rows, cols, eps);
+  return (int)cudaGetLastError();
+}
+
+template <typename T>
+static int bwd(const void* dy, const void* x, const void* w, const float* mean, const float* rstd, const void* dres,
+               void* dx, void* dw, void* db, int grad_fp32, int accumulate, float* scratch, int rows, int cols, int rms,
+               cudaStream_t st) {
+  if (cols % 8) return -1;
+  const int grid = grid_for(rows);
+  size_t smem = (size_t)cols * 4 * (rms ? 1 : 2);
+  auto k = rms ? norm_bwd_kernel<T, true> : norm_bwd_kernel<T, false>;
+  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  float* pw = scratch;
+  float* pb = scratch + (size_t)grid * cols;
+  k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,
+                                 rows, cols);
+  const int rb = (cols + 255) / 256;
+  if (grad_fp32) {
+    reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pw, (float*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pb, (float*)db, grid, cols, accumulate);
+  } else {
+    reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pw, (T*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pb, (T*)db, grid, cols, accumulate);
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace norm
+}  // namespace sb
+
+// dtype: 0 = bf16, 1 = fp32, 2 = fp16
+extern "C" int sb_norm_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out,
+                           float* mean, float* rstd, int rows, int cols, float eps, int rms, int dtype,
+                           cudaStream_t st) {
+  using namespace sb::norm;
+  if (rows <= 0) return 0;
+  if (dtype == 0) return fwd<__nv_bfloat16>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, st);
+  if (dtype == 1) return fwd<float>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, st);
+  if (dtype == 2) return fwd<__half>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, st);
+  return -2;
+}
+
+// scratch: fp32 buffer of sb_norm_bwd_scratch_floats(rows, cols, rms) elements (global memory owned by the caller)
+extern "C" long long sb_norm_bwd_scratch_floats(int rows, int cols, int rms) {
+  return (long long)sb::norm::grid_for(rows) * cols * (rms ? 1 : 2);
+}
+
+extern "C" int sb_norm_bwd(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                           const void* dres, void* dx, void* dw, void* db, int grad_fp32, int accumulate,
+                           float* scratch, int rows, int cols, int rms, int dtype, cudaStream_t st) {
+  using namespace sb::norm;
+  if (rows <= 0) return 0;
+  if (dtype == 0)
+    return bwd<__nv_bfloat16>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, scratch, rows, cols, rms, st);
+  if (dtype == 1)
+    return bwd<float>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, scratch, rows, cols, rms, st);
+  if (dtype == 2)
+    return bwd<__half>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, scratch, rows, cols, rms, st);
+  return -2;
+}

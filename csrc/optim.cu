@@ -1,0 +1,164 @@
+// Fused optimizer kernels for sm_100a (SURVEY §8 O1 single-rank part, K14–K18 replacement).
+//
+// The reference's step walks Python lists of parameters: per-parameter overflow checks with a host sync each
+// (core/optimizer/loss_scaler.py:23-41), per-parameter unscale + norm (parameter_group.py:483-535), an fp32 copy of the
+// gradients (parameter_group.py:346-410), torch.optim.AdamW on the fp32 shard (optimizer.py:179) and a cast back to the
+// model dtype (parameter_group.py:423-430).  Here the ZeRO shard is one flat arena, so the whole step is two launches:
+//   sb_grad_sumsq : Σg² and a non-finite flag over the flat gradient shard, deterministic two-stage reduction
+//   sb_adamw      : unscale · clip (coefficient derived on the device from the reduced norm, no host sync) · AdamW on
+//                   the fp32 master/m/v shard · cast to the bf16 model shard · optional gradient zeroing, in one pass.
+#include "common.cuh"
+
+namespace sb {
+namespace optim {
+
+constexpr int kThreads = 256;
+constexpr int kMaxBlocks = 148 * 8;
+
+template <typename G>
+SB_DEVICE float ldg(const G* p, size_t i) {
+  return (float)p[i];
+}
+
+// stage 1: per-block partial sums -> partial[blockIdx], non-finite -> flag
+template <typename G>
+__global__ void __launch_bounds__(kThreads) sumsq_kernel(const G* __restrict__ g, size_t n, float* __restrict__ partial,
+                                                         int* __restrict__ nonfinite) {
+  __shared__ float red[kThreads / 32];
+  float s = 0.f;
+  bool bad = false;
+  for (size_t i = blockIdx.x * (size_t)kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+    float v = (float)g[i];
+    bad |= !isfinite(v);
+    s += v * v;
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  if (__syncthreads_or(bad) && threadIdx.x == 0) atomicOr(nonfinite, 1);
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < kThreads / 32; ++i) t += red[i];
+    partial[blockIdx.x] = t;
+  }
+}
+// stage 2: fixed-order sum of the partials; out[0] (+)= total
+__global__ void sumsq_final_kernel(const float* __restrict__ partial, int parts, float* __restrict__ out, int accumulate) {
+  __shared__ float red[kThreads / 32];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < parts; i += kThreads) s += partial[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < kThreads / 32; ++i) t += red[i];
+    out[0] = accumulate ? out[0] + t : t;
+  }
+}
+
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay, bias_corr1, bias_corr2_sqrt;
+  float inv_loss_scale;  // gradients are multiplied by this (1 / loss scale)
+  float clip;            // max global norm, 0 = off
+  int zero_grad;
+};
+
+// p32/m/v: fp32 shard; g: gradient shard (G); out: model-dtype shard (P) written with the updated value.
+// norm_sq: device scalar with the *global* Σg² of the still-scaled gradients (may be null when clip == 0).
+// skip: device flag, non-zero -> leave everything untouched (overflow step).
+template <typename G, typename P>
+__global__ void __launch_bounds__(kThreads) adamw_kernel(float* __restrict__ p32, float* __restrict__ m,
+                                                         float* __restrict__ v, G* __restrict__ g, P* __restrict__ out,
+                                                         size_t n, AdamArgs a, const float* __restrict__ norm_sq,
+                                                         const int* __restrict__ skip) {
+  if (skip && *skip) return;
+  float gs = a.inv_loss_scale;
+  if (a.clip > 0.f && norm_sq) {
+    const float norm = sqrtf(*norm_sq) * a.inv_loss_scale;
+    const float coef = a.clip / (norm + 1e-6f);
+    if (coef < 1.f) gs *= coef;
+  }
+  const float step_size = a.lr / a.bias_corr1;
+  const float decay = 1.f - a.lr * a.weight_decay;
+  for (size_t i = blockIdx.x * (size_t)kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+    const float grad = (float)g[i] * gs;
+    float mi = m[i], vi = v[i], pi = p32[i];
+    mi = a.beta1 * mi + (1.f - a.beta1) * grad;
+    vi = a.beta2 * vi + (1.f - a.beta2) * grad * grad;
+    pi = pi * decay - step_size * mi / (sqrtf(vi) / a.bias_corr2_sqrt + a.eps);
+    m[i] = mi, v[i] = vi, p32[i] = pi;
+    if (out) out[i] = (P)pi;
+    if (a.zero_grad) g[i] = (G)0.f;
+  }
+}
+
+// dst (P) <- src (fp32) cast, used when refreshing the model copy from master weights
+template <typename P>
+__global__ void cast_kernel(const float* __restrict__ src, P* __restrict__ dst, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) dst[i] = (P)src[i];
+}
+
+static int blocks(size_t n) {
+  size_t b = (n + kThreads - 1) / kThreads;
+  return (int)(b < 1 ? 1 : (b > (size_t)kMaxBlocks ? kMaxBlocks : b));
+}
+
+}  // namespace optim
+}  // namespace sb
+
+using namespace sb::optim;
+
+extern "C" int sb_grad_sumsq_scratch_floats() { return kMaxBlocks; }
+
+// grad dtype: 0 bf16, 1 fp32, 2 fp16.  scratch: >= sb_grad_sumsq_scratch_floats() floats.  out[0] (+)= Σ g²;
+// *nonfinite |= any(!isfinite(g)).
+extern "C" int sb_grad_sumsq(const void* g, long long n, int dtype, float* scratch, float* out, int accumulate,
+                             int* nonfinite, cudaStream_t st) {
+  if (n <= 0) {
+    if (!accumulate) cudaMemsetAsync(out, 0, 4, st);
+    return 0;
+  }
+  const int b = blocks(n);
+  if (dtype == 0)
+    sumsq_kernel<__nv_bfloat16><<<b, kThreads, 0, st>>>((const __nv_bfloat16*)g, n, scratch, nonfinite);
+  else if (dtype == 1)
+    sumsq_kernel<float><<<b, kThreads, 0, st>>>((const float*)g, n, scratch, nonfinite);
+  else
+    sumsq_kernel<__half><<<b, kThreads, 0, st>>>((const __half*)g, n, scratch, nonfinite);
+  sumsq_final_kernel<<<1, kThreads, 0, st>>>(scratch, b, out, accumulate);
+  return (int)cudaGetLastError();
+}
+
+// grad_dtype / out_dtype: 0 bf16, 1 fp32, 2 fp16 (out may be null)
+extern "C" int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long long n, int grad_dtype, int out_dtype,
+                        float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                        float inv_loss_scale, float clip, const float* norm_sq, const int* skip, int zero_grad,
+                        cudaStream_t st) {
+  if (n <= 0) return 0;
+  AdamArgs a;
+  a.lr = lr, a.beta1 = beta1, a.beta2 = beta2, a.eps = eps, a.weight_decay = weight_decay;
+  a.bias_corr1 = 1.f - powf(beta1, (float)step);
+  a.bias_corr2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
+  a.inv_loss_scale = inv_loss_scale, a.clip = clip, a.zero_grad = zero_grad;
+  const int b = blocks(n);
+#define SB_ADAM(GT, PT) \
+  adamw_kernel<GT, PT><<<b, kThreads, 0, st>>>(p32, m, v, (GT*)g, (PT*)out, (size_t)n, a, norm_sq, skip)
+  if (grad_dtype == 0 && out_dtype == 0) SB_ADAM(__nv_bfloat16, __nv_bfloat16);
+  else if (grad_dtype == 1 && out_dtype == 0) SB_ADAM(float, __nv_bfloat16);
+  else if (grad_dtype == 1 && out_dtype == 1) SB_ADAM(float, float);
+  else if (grad_dtype == 0 && out_dtype == 1) SB_ADAM(__nv_bfloat16, float);
+  else if (grad_dtype == 2 && out_dtype == 2) SB_ADAM(__half, __half);
+  else if (grad_dtype == 1 && out_dtype == 2) SB_ADAM(float, __half);
+  else return -2;
+#undef SB_ADAM
+  return (int)cudaGetLastError();
+}
+
+extern "C" int sb_cast_from_fp32(const float* src, void* dst, long long n, int out_dtype, cudaStream_t st) {
+  if (n <= 0) return 0;
+  const int b = blocks(n);
+  if (out_dtype == 0) cast_kernel<__nv_bfloat16><<<b, kThreads, 0, st>>>(src, (__nv_bfloat16*)dst, n);
+  else if (out_dtype == 2) cast_kernel<__half><<<b, kThreads, 0, st>>>(src, (__half*)dst, n);
+  else return -2;
+  return (int)cudaGetLastError();
+}

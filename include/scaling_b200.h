@@ -1,0 +1,77 @@
+/* C ABI of the scaling_b200 native library (scaling_b200/_kernels.so, sm_100a).
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on and returns 0 on success, a CUDA
+ * error code (> 0) or a negative argument error.  None of them allocates device memory: scratch buffers, where a
+ * kernel needs one, are passed in by the caller.  dtype codes: 0 = bf16, 1 = fp32, 2 = fp16.
+ *
+ * File:line citations name the reference (marcobellagente93/scaling, paths relative to src/scaling/) behaviour each
+ * entry point replaces.
+ */
+#pragma once
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- tcgen05 GEMM family (csrc/gemm_sm100.cu) — replaces cuBLAS behind F.linear:
+ *      core/nn/linear/column_parallel_linear.py:151, row_parallel_linear.py:158, core/nn/mlp.py:157-161 ---- */
+/* D[M,N] (+)= A·Bᵀ.  a_layout/b_layout: 0 = K-major ([M,K] / [N,K] row-major), 1 = MN-major ([K,M] / [K,N]).
+ * out_dtype: 0 bf16, 1 fp32.  epilogue: 0 store, 1 accumulate into D.  bias: optional bf16 [N].  max_ctas: 0 = all SMs. */
+int sb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
+                 int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas, cudaStream_t stream);
+/* H[M,F] = silu(X·W1ᵀ) ⊙ (X·W2ᵀ), W = [W1; W2] as one [2F,K] buffer; pre (optional) keeps (gate | up) [M,2F]. */
+int sb_gemm_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
+                        int ldh, int ldpre, int max_ctas, cudaStream_t stream);
+
+/* ---- norms (csrc/norm.cu) — core/nn/norm/rms_norm.py:45-53, core/nn/norm/layernorm.py:72-79 ---- */
+int sb_norm_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
+                float* rstd, int rows, int cols, float eps, int rms, int dtype, cudaStream_t st);
+long long sb_norm_bwd_scratch_floats(int rows, int cols, int rms);
+int sb_norm_bwd(const void* dy, const void* x, const void* w, const float* mean, const float* rstd, const void* dres,
+                void* dx, void* dw, void* db, int grad_fp32, int accumulate, float* scratch, int rows, int cols,
+                int rms, int dtype, cudaStream_t st);
+
+/* ---- element-wise (csrc/elementwise.cu) — core/nn/mlp.py:157-160, core/nn/rotary.py:68-139,
+ *      transformer/model/layers/layer.py:211-216, core/nn/linear/vocab_parallel_embedding.py:119-147 ---- */
+int sb_swiglu_fwd(const void* pre, void* h, int rows, int F, cudaStream_t st);
+int sb_swiglu_bwd(const void* pre, const void* dh, void* dpre, void* h_out, int rows, int F, cudaStream_t st);
+int sb_act_fwd(const void* x, void* y, long long n, int act, cudaStream_t st);
+int sb_act_bwd(const void* x, const void* dy, void* dx, long long n, int act, cudaStream_t st);
+int sb_rope(void* x, const float* cos_t, const float* sin_t, const int* pos, int tokens, int heads, int head_dim,
+            int rot_dim, long long token_stride, int seq, int mode, int backward, cudaStream_t st);
+int sb_bias_dropout_add(const void* x, const void* bias, const void* residual, void* out, long long n, int cols,
+                        float p, unsigned long long seed, unsigned long long offset, cudaStream_t st);
+int sb_dropout_bwd(const void* dout, void* dx, long long n, float p, unsigned long long seed,
+                   unsigned long long offset, cudaStream_t st);
+int sb_embedding_fwd(const long long* ids, const void* W, void* out, int tokens, int hidden, long long vocab_start,
+                     long long vocab_end, cudaStream_t st);
+int sb_embedding_bwd(const long long* ids, const void* dout, void* dW, int grad_fp32, int tokens, int hidden,
+                     long long vocab_start, long long vocab_end, cudaStream_t st);
+
+/* ---- vocab-parallel cross-entropy (csrc/xent.cu) — transformer/model/model.py:56-76,
+ *      transformer/model/layers/lm_head_tied.py:41-43 ---- */
+int sb_xent_stats(const void* logits, const long long* targets, float* stats, int tokens, int vocab_local,
+                  long long ld, long long vocab_start, int dtype, cudaStream_t st);
+int sb_xent_grad(void* logits, const long long* targets, const float* lse, const float* coeff, const float* gscale,
+                 int tokens, int vocab_local, long long ld, long long vocab_start, int dtype, cudaStream_t st);
+
+/* ---- optimizer (csrc/optim.cu) — core/optimizer/optimizer.py:107-208, parameter_group.py:346-535,
+ *      loss_scaler.py:23-41 ---- */
+int sb_grad_sumsq_scratch_floats(void);
+int sb_grad_sumsq(const void* g, long long n, int dtype, float* scratch, float* out, int accumulate, int* nonfinite,
+                  cudaStream_t st);
+int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long long n, int grad_dtype, int out_dtype, float lr,
+             float beta1, float beta2, float eps, float weight_decay, int step, float inv_loss_scale, float clip,
+             const float* norm_sq, const int* skip, int zero_grad, cudaStream_t st);
+int sb_cast_from_fp32(const float* src, void* dst, long long n, int out_dtype, cudaStream_t st);
+
+/* ---- data (csrc/blend_index.cpp) — core/data/blended_dataset.py:316-329 (Rust wheel blended_dataset_loop),
+ *      transformer/data/text_dataset.py:371-385 ---- */
+long long sb_blend_index(const long long* counts, int n_datasets, long long* out, long long capacity);
+long long sb_gather_window_i32(const int* tokens, const long long* doc_offsets, const long long* pieces, int n_pieces,
+                               int* out, long long capacity);
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,137 @@
+"""ctypes binding of ``scaling_b200/_kernels.so`` (C ABI declared in ``include/scaling_b200.h``).
+
+The library is built in-tree by :mod:`scaling_b200.ops.build`.  On a machine with a GPU a missing or broken library
+is a hard error — the sm_100a kernels are the product, there is no silent fallback.  On a CPU-only machine
+``available()`` is False and the modules use their plain PyTorch expressions (the oracle / gloo path).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_longlong, c_ulonglong, c_void_p
+from pathlib import Path
+from typing import Optional
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parents[1] / "_kernels.so"
+_lib: Optional[ctypes.CDLL] = None
+_launches = 0  # number of kernel launches issued through this binding (bench.py reports it as gpu_launches)
+
+P = c_void_p
+_SIGS = {
+    "sb_gemm_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_norm_fwd": [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, c_int, P],
+    "sb_norm_bwd": [P, P, P, P, P, P, P, P, P, c_int, c_int, P, c_int, c_int, c_int, c_int, P],
+    "sb_swiglu_fwd": [P, P, c_int, c_int, P],
+    "sb_swiglu_bwd": [P, P, P, P, c_int, c_int, P],
+    "sb_act_fwd": [P, P, c_longlong, c_int, P],
+    "sb_act_bwd": [P, P, P, c_longlong, c_int, P],
+    "sb_rope": [P, P, P, P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, c_int, P],
+    "sb_bias_dropout_add": [P, P, P, P, c_longlong, c_int, c_float, c_ulonglong, c_ulonglong, P],
+    "sb_dropout_bwd": [P, P, c_longlong, c_float, c_ulonglong, c_ulonglong, P],
+    "sb_embedding_fwd": [P, P, P, c_int, c_int, c_longlong, c_longlong, P],
+    "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
+    "sb_xent_stats": [P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
+    "sb_xent_grad": [P, P, P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
+    "sb_grad_sumsq": [P, c_longlong, c_int, P, P, c_int, P, P],
+    "sb_adamw": [P, P, P, P, P, c_longlong, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_float,
+                 c_float, P, P, c_int, P],
+    "sb_cast_from_fp32": [P, P, c_longlong, c_int, P],
+}
+_RET_LL = {
+    "sb_norm_bwd_scratch_floats": [c_int, c_int, c_int],
+    "sb_blend_index": [P, c_int, P, c_longlong],
+    "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
+}
+_RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": []}
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def load(required: bool = False) -> Optional[ctypes.CDLL]:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.is_file():
+        if os.environ.get("SCALING_B200_AUTOBUILD", "1") == "1":
+            try:
+                from .build import build
+
+                build()
+            except Exception as e:  # noqa: BLE001
+                if required:
+                    raise RuntimeError(f"scaling_b200 native library could not be built: {e}") from e
+                return None
+        if not _LIB_PATH.is_file():
+            if required:
+                raise RuntimeError(f"{_LIB_PATH} is missing; run `python -m scaling_b200.ops.build`")
+            return None
+    lib = ctypes.CDLL(str(_LIB_PATH))
+    for name, sig in _SIGS.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.argtypes = sig
+        fn.restype = c_int
+    for name, sig in _RET_LL.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.argtypes = sig
+        fn.restype = c_longlong
+    for name, sig in _RET_INT_NOSTREAM.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.argtypes = sig
+        fn.restype = c_int
+    _lib = lib
+    return lib
+
+
+def host_lib() -> ctypes.CDLL:
+    """Library handle for the host-only (C++) entry points; usable without a GPU."""
+    lib = load(required=True)
+    assert lib is not None
+    return lib
+
+
+def available() -> bool:
+    """True when the sm_100a kernels can run: CUDA device present and the native library loads."""
+    if not torch.cuda.is_available():
+        return False
+    return load(required=True) is not None
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name: str, *args, launches: int = 1) -> None:
+    """Invoke a kernel entry point on the current stream and raise on a non-zero status."""
+    global _launches
+    lib = load(required=True)
+    rc = getattr(lib, name)(*args, stream())
+    if rc != 0:
+        raise RuntimeError(f"{name} failed with status {rc}")
+    _launches += launches
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def reset_launch_count() -> None:
+    global _launches
+    _launches = 0
+
+
+DTYPE_CODE = {torch.bfloat16: 0, torch.float32: 1, torch.float16: 2}

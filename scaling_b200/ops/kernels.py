@@ -1,0 +1,259 @@
+"""Thin tensor-level wrappers over the C ABI (no autograd here — see :mod:`scaling_b200.ops.functional`).
+
+Every wrapper checks shapes/alignment, allocates outputs with torch (so memory stays in the caching allocator) and
+launches on the current stream.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import DTYPE_CODE, call, ptr
+
+_scratch: dict[tuple, torch.Tensor] = {}
+
+
+def _scratch_buf(device: torch.device, n_floats: int, tag: str) -> torch.Tensor:
+    """Reusable fp32 scratch per (device, tag); grows geometrically, never shrinks."""
+    key = (device.index, tag)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < n_floats:
+        buf = torch.empty(max(n_floats, 1024), dtype=torch.float32, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+# ----------------------------------------------------------------------------------------------------------- GEMM
+def gemm_supported(M: int, N: int, K: int, lda: int, ldb: int, ldd: int) -> bool:
+    return M > 0 and N > 0 and K > 0 and lda % 8 == 0 and ldb % 8 == 0 and ldd % 8 == 0
+
+
+def gemm(
+    a: torch.Tensor,
+    b: torch.Tensor,
+    *,
+    a_mn: bool = False,
+    b_mn: bool = False,
+    out: Optional[torch.Tensor] = None,
+    out_dtype: torch.dtype = torch.bfloat16,
+    accumulate: bool = False,
+    bias: Optional[torch.Tensor] = None,
+    max_ctas: int = 0,
+) -> torch.Tensor:
+    """D[M,N] (+)= A · Bᵀ on the tcgen05 kernel.
+
+    a: [M,K] row-major, or [K,M] when ``a_mn``;  b: [N,K] row-major, or [K,N] when ``b_mn``.  Rows may be strided
+    (``stride(0)`` is the leading dimension) but the inner dimension must be contiguous.
+    """
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, f"inner dimensions differ: {K} vs {Kb}"
+    if out is None:
+        assert not accumulate
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
+    assert a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0 and out.data_ptr() % 16 == 0
+    lda, ldb, ldd = a.stride(0), b.stride(0), out.stride(0)
+    assert gemm_supported(M, N, K, lda, ldb, ldd), "leading dimensions must be multiples of 8 elements"
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    call(
+        "sb_gemm_bf16", ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
+        DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
+    )
+    return out
+
+
+def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """h = silu(x·W1ᵀ) ⊙ (x·W2ᵀ) with ``w_gate_up`` = [W1; W2] ([2F, K]); returns (h [M,F], pre [M,2F] or None)."""
+    assert x.dtype == torch.bfloat16 and w_gate_up.dtype == torch.bfloat16
+    M, K = x.shape
+    F2, K2 = w_gate_up.shape
+    assert K == K2 and F2 % 2 == 0 and x.stride(1) == 1 and w_gate_up.stride(1) == 1
+    F = F2 // 2
+    assert F % 8 == 0 and x.stride(0) % 8 == 0 and w_gate_up.stride(0) % 8 == 0
+    h = torch.empty((M, F), dtype=torch.bfloat16, device=x.device)
+    pre = torch.empty((M, 2 * F), dtype=torch.bfloat16, device=x.device) if keep_pre else None
+    call(
+        "sb_gemm_swiglu_bf16", ptr(x), ptr(w_gate_up), ptr(h), ptr(pre), M, F, K, x.stride(0), w_gate_up.stride(0), F,
+        2 * F, 0,
+    )
+    return h, pre
+
+
+# ----------------------------------------------------------------------------------------------------------- norms
+def norm_fwd(
+    x: torch.Tensor,
+    weight: torch.Tensor,
+    bias: Optional[torch.Tensor],
+    eps: float,
+    rms: bool,
+    residual: Optional[torch.Tensor] = None,
+) -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor], torch.Tensor]:
+    """Returns (y, x_plus_residual or None, mean or None, rstd). x: [..., cols] contiguous."""
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    assert x.is_contiguous() and cols % 8 == 0 and weight.dtype == x.dtype
+    y = torch.empty_like(x)
+    summed = torch.empty_like(x) if residual is not None else None
+    mean = None if rms else torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    if residual is not None:
+        assert residual.is_contiguous() and residual.shape == x.shape
+    call(
+        "sb_norm_fwd", ptr(x), ptr(residual), ptr(weight), ptr(bias), ptr(y), ptr(summed), ptr(mean), ptr(rstd), rows,
+        cols, float(eps), int(rms), DTYPE_CODE[x.dtype],
+    )
+    return y, summed, mean, rstd
+
+
+def norm_bwd(
+    dy: torch.Tensor,
+    x: torch.Tensor,
+    weight: torch.Tensor,
+    mean: Optional[torch.Tensor],
+    rstd: torch.Tensor,
+    rms: bool,
+    dres: Optional[torch.Tensor] = None,
+    dw_out: Optional[torch.Tensor] = None,
+    db_out: Optional[torch.Tensor] = None,
+    accumulate: bool = False,
+    has_bias: bool = False,
+) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+    """Returns (dx [+ dres], dw, db).  dw_out/db_out (+accumulate) write straight into a main-grad buffer."""
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    assert dy.is_contiguous() and x.is_contiguous()
+    dx = torch.empty_like(x)
+    dw = dw_out if dw_out is not None else torch.empty(cols, dtype=x.dtype, device=x.device)
+    db = db_out if db_out is not None else (torch.empty(cols, dtype=x.dtype, device=x.device) if has_bias else None)
+    grad_fp32 = int(dw.dtype == torch.float32)
+    lib = _lib.load(required=True)
+    n = lib.sb_norm_bwd_scratch_floats(rows, cols, int(rms))
+    scratch = _scratch_buf(x.device, n, "norm_bwd")
+    call(
+        "sb_norm_bwd", ptr(dy), ptr(x), ptr(weight), ptr(mean), ptr(rstd), ptr(dres), ptr(dx), ptr(dw), ptr(db),
+        grad_fp32, int(accumulate), ptr(scratch), rows, cols, int(rms), DTYPE_CODE[x.dtype],
+        launches=2 if (rms or db is None) else 3,
+    )
+    return dx, dw, db
+
+
+# ----------------------------------------------------------------------------------------------------------- element-wise
+def swiglu_fwd(pre: torch.Tensor) -> torch.Tensor:
+    rows, F2 = pre.shape
+    h = torch.empty((rows, F2 // 2), dtype=pre.dtype, device=pre.device)
+    call("sb_swiglu_fwd", ptr(pre), ptr(h), rows, F2 // 2)
+    return h
+
+
+def swiglu_bwd(pre: torch.Tensor, dh: torch.Tensor, recompute_h: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    rows, F2 = pre.shape
+    assert pre.is_contiguous() and dh.is_contiguous()
+    dpre = torch.empty_like(pre)
+    h = torch.empty_like(dh) if recompute_h else None
+    call("sb_swiglu_bwd", ptr(pre), ptr(dh), ptr(dpre), ptr(h), rows, F2 // 2)
+    return dpre, h
+
+
+def act_fwd(x: torch.Tensor, silu: bool) -> torch.Tensor:
+    y = torch.empty_like(x)
+    call("sb_act_fwd", ptr(x), ptr(y), x.numel(), int(silu))
+    return y
+
+
+def act_bwd(x: torch.Tensor, dy: torch.Tensor, silu: bool) -> torch.Tensor:
+    dx = torch.empty_like(x)
+    call("sb_act_bwd", ptr(x), ptr(dy), ptr(dx), x.numel(), int(silu))
+    return dx
+
+
+def rope_(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[torch.Tensor], seq: int, mode: int,
+          rot_dim: int, backward: bool = False) -> torch.Tensor:
+    """In-place rotary on x [tokens, heads, head_dim] (token stride may exceed heads*head_dim). mode 0 = interleaved
+    pairs (rotary_complex), 1 = half rotation (rotary)."""
+    assert x.dtype == torch.bfloat16 and x.dim() == 3 and x.stride(2) == 1 and x.stride(1) == x.shape[2]
+    assert cos.dtype == torch.float32 and sin.dtype == torch.float32 and cos.is_contiguous() and sin.is_contiguous()
+    if pos is not None:
+        assert pos.dtype == torch.int32 and pos.is_contiguous()
+    tokens, heads, hd = x.shape
+    call("sb_rope", ptr(x), ptr(cos), ptr(sin), ptr(pos), tokens, heads, hd, rot_dim, x.stride(0), seq, mode,
+         int(backward))
+    return x
+
+
+def bias_dropout_add(x: torch.Tensor, bias: Optional[torch.Tensor], residual: Optional[torch.Tensor], p: float,
+                     seed: int, offset: int) -> torch.Tensor:
+    assert x.is_contiguous() and x.dtype == torch.bfloat16
+    out = torch.empty_like(x)
+    call("sb_bias_dropout_add", ptr(x), ptr(bias), ptr(residual), ptr(out), x.numel(), x.shape[-1], float(p), seed,
+         offset)
+    return out
+
+
+def dropout_bwd(dout: torch.Tensor, p: float, seed: int, offset: int) -> torch.Tensor:
+    dx = torch.empty_like(dout)
+    call("sb_dropout_bwd", ptr(dout), ptr(dx), dout.numel(), float(p), seed, offset)
+    return dx
+
+
+def embedding_fwd(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int) -> torch.Tensor:
+    assert ids.dtype == torch.int64 and ids.is_contiguous() and weight.dtype == torch.bfloat16
+    out = torch.empty((*ids.shape, weight.shape[1]), dtype=weight.dtype, device=weight.device)
+    call("sb_embedding_fwd", ptr(ids), ptr(weight), ptr(out), ids.numel(), weight.shape[1], vocab_start, vocab_end)
+    return out
+
+
+def embedding_bwd(ids: torch.Tensor, dout: torch.Tensor, dweight: torch.Tensor, vocab_start: int, vocab_end: int) -> None:
+    """dweight (fp32 or bf16, [V_local, hidden]) += scatter(dout) — accumulates in place."""
+    assert dout.is_contiguous() and dweight.is_contiguous()
+    call("sb_embedding_bwd", ptr(ids), ptr(dout), ptr(dweight), int(dweight.dtype == torch.float32), ids.numel(),
+         dweight.shape[1], vocab_start, vocab_end)
+
+
+# ----------------------------------------------------------------------------------------------------------- cross-entropy
+def xent_stats(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int) -> torch.Tensor:
+    """[tokens, 4] fp32: local max, local Σexp(x-max), target logit (0 if remote), local argmax (int bits)."""
+    tokens, v = logits.shape
+    assert logits.stride(1) == 1 and targets.dtype == torch.int64 and targets.is_contiguous()
+    stats = torch.empty((tokens, 4), dtype=torch.float32, device=logits.device)
+    call("sb_xent_stats", ptr(logits), ptr(targets), ptr(stats), tokens, v, logits.stride(0), vocab_start,
+         DTYPE_CODE[logits.dtype])
+    return stats
+
+
+def xent_grad_(logits: torch.Tensor, targets: torch.Tensor, lse: torch.Tensor, coeff: torch.Tensor,
+               gscale: Optional[torch.Tensor], vocab_start: int) -> torch.Tensor:
+    """Overwrites logits with (softmax - onehot) * coeff[token] * gscale."""
+    tokens, v = logits.shape
+    assert lse.dtype == torch.float32 and coeff.dtype == torch.float32
+    call("sb_xent_grad", ptr(logits), ptr(targets), ptr(lse), ptr(coeff), ptr(gscale), tokens, v, logits.stride(0),
+         vocab_start, DTYPE_CODE[logits.dtype])
+    return logits
+
+
+# ----------------------------------------------------------------------------------------------------------- optimizer
+def grad_sumsq(g: torch.Tensor, out: torch.Tensor, nonfinite: torch.Tensor, accumulate: bool = False) -> None:
+    lib = _lib.load(required=True)
+    scratch = _scratch_buf(g.device, lib.sb_grad_sumsq_scratch_floats(), "sumsq")
+    call("sb_grad_sumsq", ptr(g), g.numel(), DTYPE_CODE[g.dtype], ptr(scratch), ptr(out), int(accumulate),
+         ptr(nonfinite), launches=2)
+
+
+def adamw_step(p32, m, v, g, out, *, lr, beta1, beta2, eps, weight_decay, step, inv_loss_scale=1.0, clip=0.0,
+               norm_sq=None, skip=None, zero_grad=False) -> None:
+    n = p32.numel()
+    assert m.numel() == n and v.numel() == n and g.numel() == n and (out is None or out.numel() == n)
+    call("sb_adamw", ptr(p32), ptr(m), ptr(v), ptr(g), ptr(out), n, DTYPE_CODE[g.dtype],
+         DTYPE_CODE[out.dtype] if out is not None else 0, float(lr), float(beta1), float(beta2), float(eps),
+         float(weight_decay), int(step), float(inv_loss_scale), float(clip), ptr(norm_sq), ptr(skip), int(zero_grad))

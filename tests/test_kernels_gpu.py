@@ -1,0 +1,261 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 expression of the same op (GPU only)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from scaling_b200.ops import _lib, kernels
+
+    assert _lib.available(), "native library must load on a GPU box"
+    return kernels
+
+
+def _rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.float(), b.float()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+@pytest.mark.parametrize(
+    "M,N,K_",
+    [(128, 256, 64), (256, 512, 128), (4096, 4096, 4096), (1000, 776, 520), (4096, 6144, 4096), (72, 40, 136), (8, 8, 8)],
+)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_layouts(K, M, N, K_, a_mn, b_mn):
+    torch.manual_seed(0)
+    dev = "cuda"
+    a = torch.randn((K_, M) if a_mn else (M, K_), device=dev, dtype=torch.bfloat16)
+    b = torch.randn((K_, N) if b_mn else (N, K_), device=dev, dtype=torch.bfloat16)
+    A = a.float().t() if a_mn else a.float()
+    B = b.float() if b_mn else b.float().t()
+    ref = A @ B
+    out = K.gemm(a, b, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    assert out.shape == (M, N)
+    assert _rel_err(out, ref) < 1e-2, _rel_err(out, ref)
+    out32 = K.gemm(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    assert _rel_err(out32, ref) < 1e-4, _rel_err(out32, ref)
+
+
+def test_gemm_accumulate_and_bias(K):
+    torch.manual_seed(1)
+    M, N, K_ = 512, 768, 320
+    a = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(N, K_, device="cuda", dtype=torch.bfloat16)
+    bias = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    ref = a.float() @ b.float().t()
+    acc = torch.randn(M, N, device="cuda", dtype=torch.float32)
+    want = acc + ref
+    K.gemm(a, b, out=acc, accumulate=True)
+    assert _rel_err(acc, want) < 1e-4
+    accb = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+    wantb = accb.float() + ref
+    K.gemm(a, b, out=accb, accumulate=True)
+    assert _rel_err(accb, wantb) < 1e-2
+    out = K.gemm(a, b, bias=bias)
+    assert _rel_err(out, ref + bias.float()) < 1e-2
+    # strided rows (views into a wider buffer), as used for fused q|k|v outputs
+    wide = torch.zeros(M, N + 64, device="cuda", dtype=torch.bfloat16)
+    K.gemm(a, b, out=wide[:, :N])
+    assert _rel_err(wide[:, :N], ref) < 1e-2 and float(wide[:, N:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("M,F,K_", [(256, 512, 256), (4096, 14336, 4096), (300, 136, 72)])
+def test_gemm_swiglu(K, M, F, K_):
+    torch.manual_seed(2)
+    x = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(2 * F, K_, device="cuda", dtype=torch.bfloat16) / math.sqrt(K_)
+    h, pre = K.gemm_swiglu(x, w)
+    g = (x.float() @ w[:F].float().t()).bfloat16().float()
+    u = (x.float() @ w[F:].float().t()).bfloat16().float()
+    ref = torch.nn.functional.silu(g) * u
+    assert _rel_err(pre[:, :F], g) < 1e-2 and _rel_err(pre[:, F:], u) < 1e-2
+    assert _rel_err(h, ref) < 2e-2
+    assert _rel_err(K.swiglu_fwd(pre), torch.nn.functional.silu(pre[:, :F].float()) * pre[:, F:].float()) < 1e-2
+
+
+@pytest.mark.parametrize("rms", [True, False])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("rows,cols", [(64, 256), (1000, 4096), (7, 8192)])
+def test_norm_fwd_bwd(K, rms, dtype, rows, cols):
+    torch.manual_seed(3)
+    x = torch.randn(rows, cols, device="cuda", dtype=dtype)
+    res = torch.randn(rows, cols, device="cuda", dtype=dtype)
+    w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype)
+    b = None if rms else (0.1 * torch.randn(cols, device="cuda")).to(dtype)
+    dy = torch.randn(rows, cols, device="cuda", dtype=dtype)
+    eps = 1e-5
+    y, summed, mean, rstd = K.norm_fwd(x, w, b, eps, rms, residual=res)
+    h = (x + res).float().requires_grad_(True)
+    wf = w.float().requires_grad_(True)
+    if rms:
+        ref = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps) * wf
+    else:
+        ref = torch.nn.functional.layer_norm(h, (cols,), wf, b.float(), eps)
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+    assert _rel_err(summed, x + res) < tol
+    assert _rel_err(y, ref) < tol
+    ref.backward(dy.float())
+    dx, dw, db = K.norm_bwd(dy, summed, w, mean, rstd, rms, has_bias=not rms)
+    assert _rel_err(dx, h.grad) < tol
+    assert _rel_err(dw, wf.grad) < tol
+    if not rms:
+        assert _rel_err(db, dy.float().sum(0)) < tol
+    # main-grad accumulation in fp32
+    main = torch.ones(cols, device="cuda", dtype=torch.float32)
+    K.norm_bwd(dy, summed, w, mean, rstd, rms, dw_out=main, accumulate=True, has_bias=False)
+    assert _rel_err(main, 1 + wf.grad) < tol
+
+
+def test_swiglu_bwd(K):
+    torch.manual_seed(4)
+    rows, F = 512, 1024
+    pre = torch.randn(rows, 2 * F, device="cuda", dtype=torch.bfloat16)
+    dh = torch.randn(rows, F, device="cuda", dtype=torch.bfloat16)
+    p = pre.float().requires_grad_(True)
+    h = torch.nn.functional.silu(p[:, :F]) * p[:, F:]
+    h.backward(dh.float())
+    dpre, hh = K.swiglu_bwd(pre, dh, recompute_h=True)
+    assert _rel_err(dpre, p.grad) < 1e-2
+    assert _rel_err(hh, h) < 1e-2
+
+
+@pytest.mark.parametrize("silu", [True, False])
+def test_activation(K, silu):
+    x = torch.randn(1024, 512, device="cuda", dtype=torch.bfloat16)
+    dy = torch.randn_like(x)
+    xf = x.float().requires_grad_(True)
+    f = torch.nn.functional.silu if silu else torch.nn.functional.gelu
+    y = f(xf)
+    y.backward(dy.float())
+    assert _rel_err(K.act_fwd(x, silu), y) < 1e-2
+    assert _rel_err(K.act_bwd(x, dy, silu), xf.grad) < 1e-2
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_rope(K, mode):
+    torch.manual_seed(5)
+    tokens, heads, hd, seq = 256, 4, 64, 128
+    rot = hd if mode == 0 else 32
+    x = torch.randn(tokens, heads, hd, device="cuda", dtype=torch.bfloat16)
+    inv = 1.0 / (10000 ** (torch.arange(0, rot, 2, device="cuda").float() / rot))
+    ang = torch.arange(seq, device="cuda").float()[:, None] * inv[None]
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    pos = (torch.arange(tokens, device="cuda") % seq).int()
+    xf = x.float()
+    c, s = cos[pos.long()][:, None, :], sin[pos.long()][:, None, :]
+    ref = xf.clone()
+    if mode == 0:
+        a, b = xf[..., 0:rot:2], xf[..., 1:rot:2]
+        ref[..., 0:rot:2] = a * c - b * s
+        ref[..., 1:rot:2] = a * s + b * c
+    else:
+        a, b = xf[..., : rot // 2], xf[..., rot // 2 : rot]
+        ref[..., : rot // 2] = a * c - b * s
+        ref[..., rot // 2 : rot] = a * s + b * c
+    y = K.rope_(x.clone(), cos, sin, pos, seq, mode, rot)
+    assert _rel_err(y, ref) < 1e-2
+    back = K.rope_(y.clone(), cos, sin, pos, seq, mode, rot, backward=True)
+    assert _rel_err(back, x) < 2e-2
+    y2 = K.rope_(x.clone(), cos, sin, None, seq, mode, rot)
+    assert torch.equal(y, y2)
+
+
+def test_bias_dropout_add(K):
+    torch.manual_seed(6)
+    x = torch.randn(512, 1024, device="cuda", dtype=torch.bfloat16)
+    r = torch.randn_like(x)
+    bias = torch.randn(1024, device="cuda", dtype=torch.bfloat16)
+    out = K.bias_dropout_add(x, bias, r, 0.0, 1, 0)
+    assert _rel_err(out, x.float() + bias.float() + r.float()) < 1e-2
+    p = 0.25
+    o1 = K.bias_dropout_add(x, None, None, p, 7, 3)
+    o2 = K.bias_dropout_add(x, None, None, p, 7, 3)
+    assert torch.equal(o1, o2)  # counter based: same (seed, offset) -> same mask
+    kept = (o1 != 0).float().mean().item()
+    assert abs(kept - (1 - p)) < 0.01
+    mask = (o1 != 0)
+    assert _rel_err(o1[mask], x.float()[mask] / (1 - p)) < 1e-2
+    dx = K.dropout_bwd(torch.ones_like(x), p, 7, 3)
+    assert torch.equal(dx != 0, mask)
+    assert not torch.equal(o1, K.bias_dropout_add(x, None, None, p, 7, 4))
+
+
+def test_embedding(K):
+    torch.manual_seed(7)
+    V, H, T = 1000, 256, 512
+    w = torch.randn(V, H, device="cuda", dtype=torch.bfloat16)
+    ids = torch.randint(0, 2 * V, (T,), device="cuda")
+    out = K.embedding_fwd(ids, w, 0, V)
+    inrange = ids < V
+    ref = torch.zeros(T, H, device="cuda")
+    ref[inrange] = w.float()[ids[inrange]]
+    assert torch.equal(out.float(), ref)
+    dout = torch.randn(T, H, device="cuda", dtype=torch.bfloat16)
+    dW = torch.zeros(V, H, device="cuda", dtype=torch.float32)
+    K.embedding_bwd(ids, dout, dW, 0, V)
+    want = torch.zeros(V, H, device="cuda")
+    want.index_add_(0, ids[inrange], dout.float()[inrange])
+    assert _rel_err(dW, want) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_cross_entropy(K, dtype):
+    torch.manual_seed(8)
+    T, V = 300, 32000
+    logits = (3 * torch.randn(T, V, device="cuda")).to(dtype)
+    targets = torch.randint(0, V, (T,), device="cuda")
+    lf = logits.float().requires_grad_(True)
+    loss_tok = torch.nn.functional.cross_entropy(lf, targets, reduction="none")
+    # two "ranks": the two halves of the vocabulary
+    halves = [logits[:, : V // 2].contiguous(), logits[:, V // 2 :].contiguous()]
+    stats = [K.xent_stats(h, targets, i * (V // 2)) for i, h in enumerate(halves)]
+    m = torch.maximum(stats[0][:, 0], stats[1][:, 0])
+    s = sum(st[:, 1] * torch.exp(st[:, 0] - m) for st in stats)
+    lse = m + torch.log(s)
+    tl = stats[0][:, 2] + stats[1][:, 2]
+    assert torch.allclose(lse - tl, loss_tok, atol=2e-3, rtol=1e-3)
+    am = torch.where(stats[0][:, 0] >= stats[1][:, 0], stats[0][:, 3].view(torch.int32), stats[1][:, 3].view(torch.int32))
+    assert torch.equal(am.long(), logits.float().argmax(-1))
+    w = torch.rand(T, device="cuda")
+    (loss_tok * w).sum().backward()
+    for i, h in enumerate(halves):
+        K.xent_grad_(h, targets, lse, w, None, i * (V // 2))
+    got = torch.cat(halves, dim=1)
+    assert _rel_err(got, lf.grad) < (2e-2 if dtype == torch.bfloat16 else 1e-4)
+
+
+@pytest.mark.parametrize("gdtype", [torch.bfloat16, torch.float32])
+def test_adamw_and_sumsq(K, gdtype):
+    torch.manual_seed(9)
+    n = 1_000_003
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda").to(gdtype)
+    ref_p = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([ref_p], lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    out = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    norm_sq = torch.zeros(1, device="cuda")
+    bad = torch.zeros(1, device="cuda", dtype=torch.int32)
+    clip = 1.0
+    for step in range(1, 4):
+        K.grad_sumsq(g, norm_sq, bad)
+        assert abs(norm_sq.item() - g.float().pow(2).sum().item()) / norm_sq.item() < 1e-4
+        coef = min(1.0, clip / (math.sqrt(norm_sq.item()) + 1e-6))
+        ref_p.grad = g.float() * coef
+        opt.step()
+        K.adamw_step(p, m, v, g, out, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, step=step,
+                     clip=clip, norm_sq=norm_sq)
+        assert _rel_err(p, ref_p.data) < 1e-5
+        assert _rel_err(out, ref_p.data) < 1e-2
+    assert bad.item() == 0
+    g[5] = float("inf")
+    K.grad_sumsq(g, norm_sq, bad)
+    assert bad.item() == 1
+    before = p.clone()
+    K.adamw_step(p, m, v, g, out, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, step=4, skip=bad)
+    assert torch.equal(p, before)
