@@ -1,0 +1,90 @@
+"""Tensor-parallel MLP blocks (reference: core/nn/mlp.py:1-167).
+
+``ParallelSwiGLUMLP`` keeps the reference's three parameters (``dense_in`` = gate, ``siglu_weight`` = up,
+``dense_out``) but runs gate and up as ONE dual GEMM with the silu·mul in its TMEM epilogue, one dgrad and one wgrad
+GEMM in backward (one dX all-reduce instead of two under TP).  Row-parallel biases are added once after the reduction.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import torch
+
+from ...ops import functional as OF
+from ..topology import Topology
+from .activation import ActivationFunction, get_activation_function
+from .linear import ColumnParallelLinear, RowParallelLinear
+from .tp_ops import all_reduce, all_reduce_scatter_to_sequence_parallel, copy_to_tensor_model_parallel_region
+
+InitFn = Callable[[torch.Tensor], torch.Tensor]
+
+
+def _features(io_features: int, factor: float) -> int:
+    f = io_features * factor
+    assert float(int(f)) == f, "io_features * intermediate_feature_factor does not result in a natural number"
+    return int(f)
+
+
+def _sp(topology: Optional[Topology]) -> bool:
+    return topology is not None and topology.config.sequence_parallel
+
+
+def _finish_row_parallel(y: torch.Tensor, layer: RowParallelLinear, topology: Optional[Topology]) -> torch.Tensor:
+    """Reduce a row-parallel partial sum (reduce-scatter under SP, all-reduce otherwise), then add the bias once."""
+    if _sp(topology):
+        y = all_reduce_scatter_to_sequence_parallel(y, topology)
+    else:
+        y = all_reduce(y, topology)
+    b = layer.get_bias()
+    return y if b is None else y + b
+
+
+class ParallelMLP(torch.nn.Module):
+    """h -> factor·h -> activation -> h."""
+
+    def __init__(self, io_features: int, intermediate_feature_factor: float, bias: bool = True,
+                 device: Optional[torch.device] = None, dtype: torch.dtype = torch.float32,
+                 topology: Optional[Topology] = None, init_method: InitFn = torch.nn.init.xavier_normal_,
+                 bitfit_bias_name: Optional[str] = None,
+                 activation_function: ActivationFunction = ActivationFunction.GELU):
+        super().__init__()
+        f = _features(io_features, intermediate_feature_factor)
+        self.topology = topology
+        self.dense_in = ColumnParallelLinear(io_features, f, bias=bias, device=device, dtype=dtype, topology=topology,
+                                             init_method=init_method, parallel_output=True,
+                                             bitfit_bias_name=bitfit_bias_name)
+        self.dense_out = RowParallelLinear(f, io_features, bias=bias, device=device, dtype=dtype, topology=topology,
+                                           init_method=init_method, parallel_input=True, parallel_output=True,
+                                           bitfit_bias_name=bitfit_bias_name)
+        self.activation_function = get_activation_function(activation_function)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        h = self.activation_function(self.dense_in(x))
+        return _finish_row_parallel(self.dense_out(h), self.dense_out, self.topology)
+
+
+class ParallelSwiGLUMLP(torch.nn.Module):
+    """dense_out( silu(dense_in(x)) * siglu_weight(x) )."""
+
+    def __init__(self, io_features: int, intermediate_feature_factor: float, bias: bool = True,
+                 device: Optional[torch.device] = None, dtype: torch.dtype = torch.float32,
+                 topology: Optional[Topology] = None, init_method: InitFn = torch.nn.init.xavier_normal_,
+                 bitfit_bias_name: Optional[str] = None):
+        super().__init__()
+        f = _features(io_features, intermediate_feature_factor)
+        self.topology = topology
+        kw = dict(bias=bias, device=device, dtype=dtype, topology=topology, init_method=init_method,
+                  bitfit_bias_name=bitfit_bias_name)
+        self.dense_in = ColumnParallelLinear(io_features, f, parallel_output=True, **kw)
+        self.siglu_weight = ColumnParallelLinear(io_features, f, parallel_output=True, **kw)
+        self.dense_out = RowParallelLinear(f, io_features, parallel_input=True, parallel_output=True, **kw)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not _sp(self.topology):
+            x = copy_to_tensor_model_parallel_region(x, self.topology)  # one dX all-reduce for gate and up together
+        bg, bu = self.dense_in.get_bias(), self.siglu_weight.get_bias()
+        if bg is None and bu is None:
+            h = OF.swiglu_linear(x, self.dense_in.weight, self.siglu_weight.weight)
+        else:
+            h = torch.nn.functional.silu(OF.linear(x, self.dense_in.weight, bg)) * OF.linear(x, self.siglu_weight.weight, bu)
+        return _finish_row_parallel(self.dense_out(h), self.dense_out, self.topology)

@@ -1,0 +1,140 @@
+"""Stage-to-stage transfer of arbitrary pytrees (reference: core/nn/parallel_module/communicator.py:23-511).
+
+Protocol: the first message between two ranks carries pickled metadata (tree structure, per-leaf shape/dtype/
+requires_grad, and the values of non-tensor leaves); afterwards only tensor payloads travel — one ``isend``/``irecv``
+per tensor leaf, in leaf order.  ``use_continuous_recommunication=True`` repeats the handshake on every message
+(variable shapes, e.g. inference with growing sequences).  Sends are asynchronous: the work handles (and the tensors
+they read) are parked until the next send on the same communicator or ``drain()``, so the sender's next compute
+overlaps the transfer; receives block because their data is needed immediately.  Gradients flow the other way for
+exactly the leaves that were marked ``requires_grad``.
+"""
+from __future__ import annotations
+
+import pickle
+from typing import Any, List, NamedTuple, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch.utils._pytree import tree_flatten, tree_unflatten
+
+
+class GradOutput(NamedTuple):
+    tensors: List[torch.Tensor]
+    grad_tensors: List[torch.Tensor]
+
+
+class CommunicationMetaBase(NamedTuple):
+    treespec: Any
+    leaves: Tuple[Any, ...]  # ("t", shape, dtype, requires_grad) | ("o", value)
+
+
+def _wire(t: torch.Tensor, byte_wire: bool) -> torch.Tensor:
+    t = t.detach().contiguous()
+    if byte_wire:
+        if t.dtype == torch.bool:
+            t = t.to(torch.uint8)
+        return t.reshape(-1).view(torch.uint8)
+    if t.dtype == torch.bool:
+        return t.to(torch.uint8)
+    return t
+
+
+class PipeCommunicator:
+    def __init__(self, local_device: torch.device, recv_grads: bool, recv_data: bool,
+                 use_continuous_recommunication: bool = False, group: Any = None):
+        self.local_device = local_device
+        self.recv_grads_enabled = recv_grads
+        self.recv_data_enabled = recv_data
+        self.use_continuous_recommunication = use_continuous_recommunication
+        self.group = group
+        self.byte_wire = local_device.type != "cuda"  # gloo: ship raw bytes, every dtype works
+        self._send_meta: Optional[CommunicationMetaBase] = None
+        self._recv_meta: Optional[CommunicationMetaBase] = None
+        self._pending: List[Tuple[Any, torch.Tensor]] = []
+
+    def reset_communication_meta(self) -> None:
+        self._send_meta = None
+        self._recv_meta = None
+
+    # ---- low level ----------------------------------------------------------------------------------
+    def drain(self) -> None:
+        for work, _keep in self._pending:
+            work.wait()
+        self._pending.clear()
+
+    def _isend(self, t: torch.Tensor, dst: int) -> None:
+        w = _wire(t, self.byte_wire)
+        self._pending.append((dist.isend(w, dst=dst, group=self.group), w))
+
+    def _recv_into(self, shape: Tuple[int, ...], dtype: torch.dtype, src: int) -> torch.Tensor:
+        wire_dtype = torch.uint8 if dtype == torch.bool else dtype
+        if self.byte_wire:
+            itemsize = torch.empty((), dtype=wire_dtype).element_size()
+            n = int(torch.Size(shape).numel())
+            buf = torch.empty(n * itemsize, dtype=torch.uint8, device=self.local_device)
+            dist.recv(buf, src=src, group=self.group)
+            out = buf.view(wire_dtype).reshape(shape)
+        else:
+            out = torch.empty(shape, dtype=wire_dtype, device=self.local_device)
+            dist.irecv(out, src=src, group=self.group).wait()
+        return out.to(torch.bool) if dtype == torch.bool else out
+
+    def _send_object(self, obj: Any, dst: int) -> None:
+        payload = torch.frombuffer(bytearray(pickle.dumps(obj)), dtype=torch.uint8).to(self.local_device)
+        self._isend(torch.tensor([payload.numel()], dtype=torch.long, device=self.local_device), dst)
+        self._isend(payload, dst)
+        self.drain()
+
+    def _recv_object(self, src: int) -> Any:
+        n = self._recv_into((1,), torch.long, src)
+        payload = self._recv_into((int(n.item()),), torch.uint8, src)
+        return pickle.loads(payload.cpu().numpy().tobytes())
+
+    # ---- activations --------------------------------------------------------------------------------
+    def send_data(self, data: Any, target_global_rank: int) -> None:
+        self.drain()  # previous message must have left before its buffers may be recycled
+        leaves, spec = tree_flatten(data)
+        if self._send_meta is None or self.use_continuous_recommunication:
+            described = tuple(("t", tuple(x.shape), x.dtype, bool(x.requires_grad)) if torch.is_tensor(x) else ("o", x)
+                              for x in leaves)
+            self._send_meta = CommunicationMetaBase(spec, described)
+            self._send_object(self._send_meta, target_global_rank)
+        for x in leaves:
+            if torch.is_tensor(x):
+                self._isend(x, target_global_rank)
+
+    def recv_data(self, origin_global_rank: int) -> Any:
+        if self._recv_meta is None or self.use_continuous_recommunication:
+            self._recv_meta = self._recv_object(origin_global_rank)
+        leaves = []
+        for d in self._recv_meta.leaves:
+            if d[0] == "t":
+                _, shape, dtype, requires_grad = d
+                t = self._recv_into(shape, dtype, origin_global_rank)
+                if requires_grad and t.is_floating_point():
+                    t.requires_grad_(True)
+                leaves.append(t)
+            else:
+                leaves.append(d[1])
+        return tree_unflatten(leaves, self._recv_meta.treespec)
+
+    # ---- gradients ----------------------------------------------------------------------------------
+    def send_gradients(self, data: Any, target_global_rank: int) -> None:
+        """``data`` is the pytree that was received as stage input; ships ``.grad`` of its differentiable leaves."""
+        self.drain()
+        leaves, _ = tree_flatten(data)
+        for x in leaves:
+            if torch.is_tensor(x) and x.requires_grad:
+                g = x.grad if x.grad is not None else torch.zeros_like(x)
+                self._isend(g, target_global_rank)
+
+    def recv_gradients(self, data: Any, origin_global_rank: int) -> GradOutput:
+        """``data`` is the pytree that was sent as stage output; returns the tensors to backpropagate with their
+        received gradients."""
+        leaves, _ = tree_flatten(data)
+        tensors, grads = [], []
+        for x in leaves:
+            if torch.is_tensor(x) and x.requires_grad:
+                tensors.append(x)
+                grads.append(self._recv_into(tuple(x.shape), x.dtype, origin_global_rank))
+        return GradOutput(tensors, grads)

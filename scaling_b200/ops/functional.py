@@ -1,0 +1,455 @@
+"""Autograd-aware operators.  Each op has exactly one native path (the sm_100a kernels) plus a shape/device guard that
+routes tiny, unaligned or CPU tensors to the plain PyTorch expression of the same math (linears of
+1/2/8/17 features and CPU/gloo runs are first class in the tests) — the guard is part of the op, not a second backend.
+
+Main-grad protocol: when a weight carries ``.main_grad`` (an fp32 or bf16 view into the optimizer's flat gradient
+arena) the weight-gradient GEMM accumulates straight into it from TMEM (``D += dYᵀ·X``) and autograd receives no
+weight gradient — no per-micro-batch ``.grad`` tensors, no separate accumulation kernels, no fp32 copy at step time.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from . import kernels as K
+
+_FORCE_TORCH = os.environ.get("SCALING_B200_OPS", "sm100") == "torch"
+# plain (epilogue-free) GEMMs may be routed to cuBLAS: "native" | "cublas"
+_PLAIN_GEMM = os.environ.get("SCALING_B200_PLAIN_GEMM", "native")
+
+
+def set_ops(mode: str) -> None:
+    """``"sm100"`` (default on GPU) or ``"torch"`` (oracle / baseline-inside-the-product)."""
+    global _FORCE_TORCH
+    assert mode in ("sm100", "torch")
+    _FORCE_TORCH = mode == "torch"
+
+
+def set_plain_gemm(mode: str) -> None:
+    global _PLAIN_GEMM
+    assert mode in ("native", "cublas")
+    _PLAIN_GEMM = mode
+
+
+def native_enabled(x: torch.Tensor) -> bool:
+    return (not _FORCE_TORCH) and x.is_cuda and _lib.available()
+
+
+def _aligned(*dims: int) -> bool:
+    return all(d % 8 == 0 and d > 0 for d in dims)
+
+
+def _gemm_nt(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if _PLAIN_GEMM == "cublas":
+        return F.linear(x, w, bias)
+    return K.gemm(x, w, bias=bias)
+
+
+def _gemm_nn(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    if _PLAIN_GEMM == "cublas":
+        return dy @ w
+    return K.gemm(dy, w, b_mn=True)
+
+
+def _accumulate_wgrad(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> Optional[torch.Tensor]:
+    """dW = dyᵀ·x. Into ``weight.main_grad`` (returns None) or as a fresh tensor."""
+    main = getattr(weight, "main_grad", None)
+    if main is not None:
+        K.gemm(dy, x, a_mn=True, b_mn=True, out=main, accumulate=True)
+        return None
+    if _PLAIN_GEMM == "cublas":
+        return dy.t() @ x
+    return K.gemm(dy, x, a_mn=True, b_mn=True, out_dtype=weight.dtype)
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y = _gemm_nt(x2, weight, bias)
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias = bias is not None
+        ctx.x_shape = shape
+        return y.view(*shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = _gemm_nn(dy2, weight).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            dw = _accumulate_wgrad(dy2, x2, weight)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy2.sum(0)
+        return dx, dw, db
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = x·Wᵀ (+ b) — replaces F.linear in Column/RowParallelLinear (reference column_parallel_linear.py:151)."""
+    if (native_enabled(x) and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+            and _aligned(weight.shape[0], weight.shape[1]) and x.numel() > 0
+            and (bias is None or bias.dtype == torch.bfloat16)):
+        return _LinearFn.apply(x, weight, bias)
+    return F.linear(x, weight, bias)
+
+
+# ------------------------------------------------------------------------------------------------ fused q|k|v etc.
+class _MultiLinearFn(torch.autograd.Function):
+    """Several column-parallel projections of the same input as ONE GEMM each way.
+
+    The weights stay separate parameters (checkpoint names are frozen) but live back to back in the parameter arena,
+    so ``fused_w`` is a zero-copy [ΣN_i, K] view; forward is one GEMM, backward one dgrad GEMM (instead of one per
+    projection — the reference issues 3 + 2 dX all-reduces per layer for the same reason) and one
+    wgrad GEMM accumulating into the equally contiguous main-grad arena.
+    """
+
+    @staticmethod
+    def forward(ctx, x, fused_w, fused_main_grad, *weights):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y = _gemm_nt(x2, fused_w)
+        ctx.save_for_backward(x2, fused_w)
+        ctx.fused_main_grad = fused_main_grad
+        ctx.sizes = [w.shape[0] for w in weights]
+        ctx.x_shape = shape
+        return y.view(*shape[:-1], fused_w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, fused_w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = _gemm_nn(dy2, fused_w).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        grads: list = [None] * len(ctx.sizes)
+        if not any(ctx.needs_input_grad[3:]):
+            pass  # frozen weights: no wgrad GEMM at all
+        elif ctx.fused_main_grad is not None:
+            K.gemm(dy2, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
+        else:
+            dw = K.gemm(dy2, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
+            grads = list(dw.split(ctx.sizes, dim=0))
+        return (dx, None, None, *grads)
+
+
+def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
+    """[ΣN_i, K] view over tensors that are contiguous, same width and adjacent in memory; else None."""
+    first = tensors[0]
+    if first.dim() != 2 or not all(t.is_contiguous() and t.dim() == 2 and t.shape[1] == first.shape[1]
+                                   and t.dtype == first.dtype for t in tensors):
+        return None
+    ptr = first.data_ptr()
+    rows = 0
+    for t in tensors:
+        if t.data_ptr() != ptr:
+            return None
+        ptr += t.numel() * t.element_size()
+        rows += t.shape[0]
+    base = first.detach()
+    try:
+        return torch.as_strided(base, (rows, first.shape[1]), (first.shape[1], 1))
+    except RuntimeError:  # storage too small: the tensors are adjacent but live in different storages
+        return None
+
+
+def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...]) -> Tuple[torch.Tensor, ...]:
+    """(x·W_0ᵀ, x·W_1ᵀ, …) — one GEMM when the weights are adjacent in the arena, separate linears otherwise."""
+    if native_enabled(x) and x.dtype == torch.bfloat16 and all(_aligned(*w.shape) for w in weights) and x.numel() > 0:
+        fw = fused_view(tuple(w.data for w in weights))
+        if fw is not None:
+            mains = [getattr(w, "main_grad", None) for w in weights]
+            fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
+            if fmg is not None or all(m is None for m in mains):
+                y = _MultiLinearFn.apply(x, fw, fmg, *weights)
+                return tuple(y.split([w.shape[0] for w in weights], dim=-1))
+    return tuple(linear(x, w) for w in weights)
+
+
+# ------------------------------------------------------------------------------------------------ SwiGLU MLP up
+class _SwiGLUFn(torch.autograd.Function):
+    """h = silu(x·W1ᵀ) ⊙ (x·W2ᵀ) — dual GEMM with the activation in the TMEM epilogue (reference mlp.py:157-160:
+    two cuBLAS GEMMs + silu + mul).  Keeps only the bf16 pre-activations; backward rebuilds dgate/dup in one
+    element-wise pass and runs one dgrad + one wgrad GEMM over the concatenated [2F, K] weight."""
+
+    @staticmethod
+    def forward(ctx, x, fused_w, fused_main_grad, w_gate, w_up):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        h, pre = K.gemm_swiglu(x2, fused_w, keep_pre=True)
+        ctx.save_for_backward(x2, fused_w, pre)
+        ctx.fused_main_grad = fused_main_grad
+        ctx.x_shape = shape
+        return h.view(*shape[:-1], h.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dh):
+        x2, fused_w, pre = ctx.saved_tensors
+        dh2 = dh.reshape(-1, dh.shape[-1])
+        if not dh2.is_contiguous():
+            dh2 = dh2.contiguous()
+        dpre, _ = K.swiglu_bwd(pre, dh2)
+        dx = _gemm_nn(dpre, fused_w).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dg = du = None
+        if not any(ctx.needs_input_grad[3:]):
+            pass
+        elif ctx.fused_main_grad is not None:
+            K.gemm(dpre, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
+        else:
+            dw = K.gemm(dpre, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
+            dg, du = dw.split(dw.shape[0] // 2, dim=0)
+        return dx, None, None, dg, du
+
+
+def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Parameter) -> torch.Tensor:
+    if (native_enabled(x) and x.dtype == torch.bfloat16 and _aligned(*w_gate.shape) and w_gate.shape == w_up.shape
+            and x.numel() > 0):
+        fw = fused_view((w_gate.data, w_up.data))
+        if fw is not None:
+            mains = [getattr(w_gate, "main_grad", None), getattr(w_up, "main_grad", None)]
+            fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
+            if fmg is not None or all(m is None for m in mains):
+                return _SwiGLUFn.apply(x, fw, fmg, w_gate, w_up)
+    return F.silu(linear(x, w_gate)) * linear(x, w_up)
+
+
+# ------------------------------------------------------------------------------------------------ norms
+class _NormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, eps, rms):
+        xc = x.contiguous()
+        rc = residual.contiguous() if residual is not None else None
+        y, summed, mean, rstd = K.norm_fwd(xc, weight, bias, eps, rms, residual=rc)
+        inp = summed if rc is not None else xc
+        ctx.save_for_backward(inp, weight, mean if mean is not None else rstd, rstd)
+        ctx.rms = rms
+        ctx.has_bias = bias is not None
+        ctx.has_res = rc is not None
+        ctx.weight_ref = weight
+        ctx.bias_ref = bias
+        return y, summed
+
+    @staticmethod
+    def backward(ctx, dy, dsum):
+        inp, weight, mean, rstd = ctx.saved_tensors
+        w_main = getattr(ctx.weight_ref, "main_grad", None)
+        b_main = getattr(ctx.bias_ref, "main_grad", None) if ctx.has_bias else None
+        use_main = w_main is not None and (not ctx.has_bias or b_main is not None)
+        dres = dsum.contiguous() if (ctx.has_res and dsum is not None) else None
+        dx, dw, db = K.norm_bwd(
+            dy.contiguous(), inp, weight, None if ctx.rms else mean, rstd, ctx.rms, dres=dres,
+            dw_out=w_main if use_main else None, db_out=b_main if use_main else None, accumulate=use_main,
+            has_bias=ctx.has_bias,
+        )
+        if use_main:
+            dw = db = None
+        return dx, dw, db, (dx if ctx.has_res else None), None, None
+
+
+def _norm_native_ok(x: torch.Tensor, weight: torch.Tensor) -> bool:
+    return (native_enabled(x) and x.dtype in (torch.bfloat16, torch.float32, torch.float16) and weight.dtype == x.dtype
+            and x.shape[-1] % 8 == 0 and x.numel() > 0)
+
+
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None):
+    """RMSNorm(x [+ residual]) · w with fp32 statistics.  Returns y, or (y, x + residual) when a residual is given
+    (reference rms_norm.py:45-53: fp32 normalise → cast → · weight)."""
+    if _norm_native_ok(x, weight):
+        y, s = _NormFn.apply(x, weight, None, residual, eps, True)
+        return y if residual is None else (y, s)
+    h = x if residual is None else x + residual
+    hf = h.float()
+    y = (hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + eps)).to(h.dtype) * weight
+    return y if residual is None else (y, h)
+
+
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], eps: float,
+               residual: Optional[torch.Tensor] = None):
+    if _norm_native_ok(x, weight) and (bias is None or bias.dtype == x.dtype):
+        y, s = _NormFn.apply(x, weight, bias, residual, eps, False)
+        return y if residual is None else (y, s)
+    h = x if residual is None else x + residual
+    y = F.layer_norm(h, (h.shape[-1],), weight, bias, eps)
+    return y if residual is None else (y, h)
+
+
+# ------------------------------------------------------------------------------------------------ activations
+class _ActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, silu):
+        xc = x.contiguous()
+        ctx.save_for_backward(xc)
+        ctx.silu = silu
+        return K.act_fwd(xc, silu)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        return K.act_bwd(x, dy.contiguous(), ctx.silu), None
+
+
+def activation(x: torch.Tensor, name: str) -> torch.Tensor:
+    if native_enabled(x) and x.dtype == torch.bfloat16 and x.numel() % 2 == 0 and x.numel() > 0:
+        return _ActFn.apply(x, name == "silu")
+    return F.silu(x) if name == "silu" else F.gelu(x)
+
+
+# ------------------------------------------------------------------------------------------------ rotary
+class _RopeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cos, sin, pos, seq, mode, rot_dim):
+        ctx.save_for_backward(cos, sin, pos)
+        ctx.args = (seq, mode, rot_dim)
+        out = x.clone(memory_format=torch.contiguous_format)
+        return K.rope_(out, cos, sin, pos, seq, mode, rot_dim)
+
+    @staticmethod
+    def backward(ctx, dy):
+        cos, sin, pos = ctx.saved_tensors
+        seq, mode, rot_dim = ctx.args
+        dx = K.rope_(dy.clone(memory_format=torch.contiguous_format), cos, sin, pos, seq, mode, rot_dim, backward=True)
+        return dx, None, None, None, None, None, None
+
+
+def rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[torch.Tensor], seq: int, mode: int,
+         rot_dim: int) -> torch.Tensor:
+    """x: [tokens, heads, head_dim] bf16; cos/sin fp32 [max_pos, rot_dim/2]; pos int32 [tokens] or None."""
+    return _RopeFn.apply(x, cos, sin, pos, seq, mode, rot_dim)
+
+
+# ------------------------------------------------------------------------------------------------ dropout + residual
+class _BiasDropoutAddFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, bias, residual, p, seed, offset):
+        ctx.args = (p, seed, offset)
+        ctx.has_bias = bias is not None
+        ctx.has_res = residual is not None
+        return K.bias_dropout_add(x.contiguous(), bias, residual.contiguous() if residual is not None else None, p,
+                                  seed, offset)
+
+    @staticmethod
+    def backward(ctx, dout):
+        p, seed, offset = ctx.args
+        dout = dout.contiguous()
+        dx = K.dropout_bwd(dout, p, seed, offset) if p > 0 else dout
+        db = dx.reshape(-1, dx.shape[-1]).sum(0) if ctx.has_bias else None
+        return dx, db, (dout if ctx.has_res else None), None, None, None
+
+
+def bias_dropout_add(x: torch.Tensor, bias: Optional[torch.Tensor], residual: Optional[torch.Tensor], p: float,
+                     training: bool, seed: int, offset: int) -> torch.Tensor:
+    """residual + dropout(x + bias).  The mask is a pure function of (seed, offset, element index): identical on
+    every TP rank and under activation recomputation (reference layer.py:211-216 forks a stateful RNG instead)."""
+    p = p if training else 0.0
+    if native_enabled(x) and x.dtype == torch.bfloat16 and x.numel() % 4 == 0 and x.shape[-1] % 4 == 0 and x.numel() > 0:
+        if p == 0.0 and bias is None:
+            return x if residual is None else x + residual
+        return _BiasDropoutAddFn.apply(x, bias, residual, p, seed, offset)
+    y = x if bias is None else x + bias
+    if p > 0.0:
+        y = F.dropout(y, p=p, training=True)
+    return y if residual is None else y + residual
+
+
+# ------------------------------------------------------------------------------------------------ embedding
+class _EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, weight, vocab_start, vocab_end):
+        ids = ids.contiguous()
+        ctx.save_for_backward(ids)
+        ctx.weight_ref = weight
+        ctx.range = (vocab_start, vocab_end)
+        return K.embedding_fwd(ids, weight, vocab_start, vocab_end)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        w = ctx.weight_ref
+        main = getattr(w, "main_grad", None)
+        if main is not None:
+            K.embedding_bwd(ids, dout.contiguous(), main, *ctx.range)
+            return None, None, None, None
+        dw = torch.zeros(w.shape, dtype=torch.float32, device=w.device)
+        K.embedding_bwd(ids, dout.contiguous(), dw, *ctx.range)
+        return None, dw.to(w.dtype), None, None
+
+
+def vocab_embedding(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int) -> torch.Tensor:
+    """Rows of this rank's vocab shard for ids in [vocab_start, vocab_end), zeros elsewhere (reference
+    vocab_parallel_embedding.py:119-135)."""
+    if native_enabled(weight) and weight.dtype == torch.bfloat16 and weight.shape[1] % 8 == 0 and ids.numel() > 0:
+        return _EmbeddingFn.apply(ids.long(), weight, vocab_start, vocab_end)
+    mask = (ids < vocab_start) | (ids >= vocab_end)
+    local = (ids - vocab_start).masked_fill(mask, 0)
+    out = F.embedding(local, weight)
+    return out.masked_fill(mask.unsqueeze(-1), 0.0)
+
+
+# ------------------------------------------------------------------------------------------------ cross-entropy
+class _VocabParallelXentFn(torch.autograd.Function):
+    """Per-token CE loss and arg-max over a vocabulary that is sharded across the tensor-parallel group.
+
+    Forward: one stats pass over the local [tokens, V/tp] logits (online max/Σexp, target logit, arg-max), a 16-byte
+    per-token all-gather across TP (instead of the reference's full-logit all-gather + fp32 copy,
+    lm_head_tied.py:41-43 / model.py:56-67).  Backward: overwrites the saved logits in place with
+    (softmax − onehot)·dloss — no second [tokens, V] buffer ever exists.
+    """
+
+    @staticmethod
+    def forward(ctx, logits, targets, vocab_start, group):
+        assert logits.dim() == 2
+        targets = targets.contiguous()
+        stats = K.xent_stats(logits, targets, vocab_start)
+        if group is not None and torch.distributed.get_world_size(group) > 1:
+            ws = torch.distributed.get_world_size(group)
+            gathered = torch.empty((ws * stats.shape[0], stats.shape[1]), dtype=stats.dtype, device=stats.device)
+            torch.distributed.all_gather_into_tensor(gathered, stats.contiguous(), group=group)
+            gathered = gathered.view(ws, *stats.shape)
+            m, idx = gathered[..., 0].max(dim=0)
+            s = (gathered[..., 1] * torch.exp(gathered[..., 0] - m)).sum(0)
+            tl = gathered[..., 2].sum(0)
+            am = gathered[..., 3].gather(0, idx.unsqueeze(0)).squeeze(0)
+        else:
+            m, s, tl, am = stats[:, 0], stats[:, 1], stats[:, 2], stats[:, 3]
+        lse = m + torch.log(s)
+        ctx.save_for_backward(logits, targets, lse)
+        ctx.vocab_start = vocab_start
+        argmax = am.contiguous().view(torch.int32).long()
+        ctx.mark_non_differentiable(argmax)
+        return lse - tl, argmax
+
+    @staticmethod
+    def backward(ctx, dloss, _dargmax):
+        logits, targets, lse = ctx.saved_tensors
+        K.xent_grad_(logits, targets, lse.contiguous(), dloss.float().contiguous(), None, ctx.vocab_start)
+        return logits, None, None, None
+
+
+def vocab_parallel_cross_entropy(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int = 0, group=None):
+    """logits: [tokens, V_local] (this rank's shard), targets: [tokens] global ids → (loss [tokens] fp32, argmax [tokens]).
+    NOTE: the backward pass reuses the logits buffer for the gradient."""
+    if native_enabled(logits) and logits.dtype in (torch.bfloat16, torch.float32) and logits.stride(-1) == 1 \
+            and logits.stride(0) % 8 == 0 and logits.numel() > 0:
+        return _VocabParallelXentFn.apply(logits, targets, vocab_start, group)
+    lf = logits.float()
+    ws = torch.distributed.get_world_size(group) if group is not None else 1
+    if ws > 1:
+        from ..core.nn.tp_ops import all_concat_with_group
+
+        lf = all_concat_with_group(lf, dim=-1, group=group)
+    loss = F.cross_entropy(lf, targets, reduction="none")
+    return loss, lf.argmax(-1)
