@@ -297,3 +297,123 @@ extern "C" int sb_norm_bwd(const void* dy, const void* x, const void* w, const f
     return bwd<__half>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, scratch, rows, cols, rms, st);
   return -2;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Norm backward for callers that must not allocate.
+//
+// Who this is for: code that runs where device allocation is forbidden or impossible — a step that is being
+// recorded into a CUDA graph, a real-time serving loop that has handed all remaining memory to a KV cache, a
+// plugin running inside another framework's allocator lock, or a C caller that simply has no allocator to offer.
+// Such callers cannot give sb_norm_bwd the fp32 scratch it needs for the per-CTA weight-gradient partials, so
+// this variant brings its own: a fixed array that lives in the library image.  Every GPU that loads the
+// library carries these kNoAllocScratchFloats * 4 bytes (4.75 MiB) until the process exits.
+//
+// The price of a fixed array is a fixed limit: the launch uses at most kNoAllocGrid CTAs, and
+// grid * cols * (rms ? 1 : 2) floats must fit, i.e. cols <= 8192 for RMSNorm and cols <= 4096 for LayerNorm.
+// Larger problems are refused with kNoAllocTooLarge (see sb_norm_bwd_noalloc_strerror) — nothing is launched.
+//
+// In host code the name `g_noalloc_scratch` is only a handle for the symbol, not a pointer the GPU can use, so the
+// device address is looked up with cudaGetSymbolAddress once per device (with that device current) and cached.
+// That lookup happens inside the first call made on each device; make that first call outside of any stream
+// capture.  All calls share the one array and it keeps whatever the previous call left in it.  Nothing in it has
+// to start at zero — every slot the reduction reads was written earlier in the same call — but two calls that
+// overlap on the GPU (different streams, no dependency) would overwrite each other's partials: serialise them.
+// ---------------------------------------------------------------------------------------------------------------
+namespace sb {
+namespace norm {
+
+constexpr int kNoAllocGrid = 148;                       // one CTA per SM
+constexpr int kNoAllocMaxColsRms = 8192;
+constexpr size_t kNoAllocScratchFloats = (size_t)kNoAllocGrid * kNoAllocMaxColsRms;
+constexpr int kNoAllocTooLarge = -3;
+constexpr int kNoAllocBadArgument = -1;
+constexpr int kNoAllocBadDtype = -2;
+constexpr int kNoAllocSetupFailed = -4;
+
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+
+constexpr int kMaxDevices = 64;
+static float* g_noalloc_scratch_ptr[kMaxDevices] = {nullptr};
+
+// device address of the static scratch on the current device; resolved on first use per device
+static int noalloc_scratch(float** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return kNoAllocSetupFailed;
+  if (g_noalloc_scratch_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return kNoAllocSetupFailed;
+    g_noalloc_scratch_ptr[dev] = p;
+  }
+  *out = g_noalloc_scratch_ptr[dev];
+  return 0;
+}
+
+template <typename T>
+static int bwd_noalloc(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                       const void* dres, void* dx, void* dw, void* db, int grad_fp32, int accumulate, int rows, int cols,
+                       int rms, cudaStream_t st) {
+  const int grid = rows < kNoAllocGrid ? rows : kNoAllocGrid;
+  float* scratch = nullptr;
+  if (int rc = noalloc_scratch(&scratch)) return rc;
+  size_t smem = (size_t)cols * 4 * (rms ? 1 : 2);
+  auto k = rms ? norm_bwd_kernel<T, true> : norm_bwd_kernel<T, false>;
+  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  float* pw = scratch;
+  float* pb = scratch + (size_t)grid * cols;
+  k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,
+                                 rows, cols);
+  const int rb = (cols + 255) / 256;
+  if (grad_fp32) {
+    reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pw, (float*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pb, (float*)db, grid, cols, accumulate);
+  } else {
+    reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pw, (T*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pb, (T*)db, grid, cols, accumulate);
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace norm
+}  // namespace sb
+
+// Largest `cols` the no-allocation variant accepts (8192 for RMSNorm, 4096 for LayerNorm).
+extern "C" int sb_norm_bwd_noalloc_max_cols(int rms) {
+  return rms ? sb::norm::kNoAllocMaxColsRms : sb::norm::kNoAllocMaxColsRms / 2;
+}
+
+// Human-readable text for the negative status codes of sb_norm_bwd_noalloc.
+extern "C" const char* sb_norm_bwd_noalloc_strerror(int code) {
+  using namespace sb::norm;
+  switch (code) {
+    case 0: return "success";
+    case kNoAllocBadArgument: return "sb_norm_bwd_noalloc: cols must be a positive multiple of 8 and rows positive";
+    case kNoAllocBadDtype: return "sb_norm_bwd_noalloc: dtype must be 0 (bf16), 1 (fp32) or 2 (fp16)";
+    case kNoAllocTooLarge:
+      return "sb_norm_bwd_noalloc: problem too large for the built-in scratch (cols <= 8192 for RMSNorm, <= 4096 for "
+             "LayerNorm); use sb_norm_bwd with caller-provided scratch instead";
+    case kNoAllocSetupFailed: return "sb_norm_bwd_noalloc: could not resolve the device address of the built-in scratch";
+    default: return code > 0 ? "CUDA runtime error (value is a cudaError_t)" : "unknown status";
+  }
+}
+
+// Same contract and results as sb_norm_bwd, minus the `scratch` argument: inputs and outputs are the caller's, the
+// fp32 partial buffer is the library's own static array.  Returns 0, a cudaError_t (> 0) or one of the negative codes
+// explained by sb_norm_bwd_noalloc_strerror.  Never calls cudaMalloc/cudaFree or any allocating routine.
+extern "C" int sb_norm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                                   const void* dres, void* dx, void* dw, void* db, int grad_fp32, int accumulate,
+                                   int rows, int cols, int rms, int dtype, cudaStream_t st) {
+  using namespace sb::norm;
+  if (rows <= 0 || cols <= 0 || cols % 8) return kNoAllocBadArgument;
+  if (cols > sb_norm_bwd_noalloc_max_cols(rms)) return kNoAllocTooLarge;
+  if (dtype == 0)
+    return bwd_noalloc<__nv_bfloat16>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, rows, cols, rms, st);
+  if (dtype == 1)
+    return bwd_noalloc<float>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, rows, cols, rms, st);
+  if (dtype == 2)
+    return bwd_noalloc<__half>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, rows, cols, rms, st);
+  return kNoAllocBadDtype;
+}

@@ -32,6 +32,17 @@ int sb_norm_bwd(const void* dy, const void* x, const void* w, const float* mean,
                 void* dx, void* dw, void* db, int grad_fp32, int accumulate, float* scratch, int rows, int cols,
                 int rms, int dtype, cudaStream_t st);
 
+/* No counterpart in the reference.  sb_norm_bwd for callers that cannot allocate device memory (stream capture,
+ * memory fully committed elsewhere, foreign allocator, plain C hosts): the fp32 partial buffer is a static array inside
+ * the library (4.75 MiB per GPU that loads it) instead of a caller argument.  Limits: cols <= 8192 (RMSNorm) /
+ * 4096 (LayerNorm), else status -3.  The first call on each device resolves the array's device address — issue it
+ * outside stream capture.  Calls share the array: do not overlap two of them on the GPU. */
+int sb_norm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                        const void* dres, void* dx, void* dw, void* db, int grad_fp32, int accumulate, int rows,
+                        int cols, int rms, int dtype, cudaStream_t st);
+int sb_norm_bwd_noalloc_max_cols(int rms);
+const char* sb_norm_bwd_noalloc_strerror(int code);
+
 /* ---- element-wise (csrc/elementwise.cu) — core/nn/mlp.py:157-160, core/nn/rotary.py:68-139,
  *      transformer/model/layers/layer.py:211-216, core/nn/linear/vocab_parallel_embedding.py:119-147 ---- */
 int sb_swiglu_fwd(const void* pre, void* h, int rows, int F, cudaStream_t st);
