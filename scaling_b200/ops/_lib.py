@@ -35,6 +35,9 @@ _SIGS = {
     "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
     "sb_xent_stats": [P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_xent_grad": [P, P, P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
+    "sb_attention_fwd": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float, c_int, P],
+    "sb_attention_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
+                         c_float, c_int, P],
     "sb_grad_sumsq": [P, c_longlong, c_int, P, P, c_int, P, P],
     "sb_adamw": [P, P, P, P, P, c_longlong, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_float,
                  c_float, P, P, c_int, P],

@@ -259,3 +259,33 @@ def test_adamw_and_sumsq(K, gdtype):
     before = p.clone()
     K.adamw_step(p, m, v, g, out, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, step=4, skip=bad)
     assert torch.equal(p, before)
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T,cu,heads,kv_heads", [
+    (1024, [0, 1024], 4, 4),
+    (1024, [0, 200, 512, 1024], 4, 2),
+    (1000, [0, 37, 640, 1000], 8, 1),
+    (4096, [0, 4096], 2, 1),
+])
+def test_attention_sm100(causal, T, cu, heads, kv_heads):
+    from scaling_b200.ops.attention import attention_dense
+    from scaling_b200.ops.attention_sm100 import AttentionFn
+
+    torch.manual_seed(10)
+    dev = "cuda"
+    q = torch.randn(T, heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(T, kv_heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(T, kv_heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    cu_t = torch.tensor(cu, device=dev, dtype=torch.int32)
+    scale = 1.0 / math.sqrt(128)
+    out = AttentionFn.apply(q, k, v, cu_t, max(b - a for a, b in zip(cu[:-1], cu[1:])), causal, scale)
+    qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    ref = attention_dense(qf, kf, vf, cu_t, cu_t, causal, scale)
+    assert _rel_err(out, ref) < 2e-2, _rel_err(out, ref)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    ref.backward(dout.float())
+    assert _rel_err(q.grad, qf.grad) < 3e-2, _rel_err(q.grad, qf.grad)
+    assert _rel_err(k.grad, kf.grad) < 3e-2, _rel_err(k.grad, kf.grad)
+    assert _rel_err(v.grad, vf.grad) < 3e-2, _rel_err(v.grad, vf.grad)

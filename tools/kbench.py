@@ -156,3 +156,33 @@ res["fused"].append(r)
 
 Path("gpurun_out").mkdir(exist_ok=True)
 json.dump(res, open("gpurun_out/kbench.json", "w"), indent=1)
+
+# attention forward / backward vs flash-attn (library)
+try:
+    from flash_attn import flash_attn_varlen_func
+
+    from scaling_b200.ops.attention_sm100 import AttentionFn
+
+    res["attention"] = []
+    for (Tt, heads, kvh) in [(4096, 32, 8), (8192, 32, 8)]:
+        q = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        k = torch.randn(Tt, kvh, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        v = torch.randn(Tt, kvh, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        cu = torch.tensor([0, Tt], device=dev, dtype=torch.int32)
+        sc = 128 ** -0.5
+        do = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16)
+        ours_f = timeit(lambda: AttentionFn.apply(q, k, v, cu, Tt, True, sc))
+        lib_f = timeit(lambda: flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=True))
+        o1 = AttentionFn.apply(q, k, v, cu, Tt, True, sc)
+        o2 = flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=True)
+        ours_b = timeit(lambda: torch.autograd.grad(o1, (q, k, v), do, retain_graph=True))
+        lib_b = timeit(lambda: torch.autograd.grad(o2, (q, k, v), do, retain_graph=True))
+        fl = 4.0 * Tt * Tt * heads * 128 / 2
+        r = {"name": f"attn_causal_T{Tt}_h{heads}_kv{kvh}", "fwd_ours_ms": ours_f, "fwd_lib_ms": lib_f, "fwd_ours_tflops": fl / ours_f / 1e9,
+             "fwd_lib_tflops": fl / lib_f / 1e9, "bwd_ours_ms": ours_b, "bwd_lib_ms": lib_b, "bwd_ours_tflops": 2.5 * fl / ours_b / 1e9,
+             "bwd_lib_tflops": 2.5 * fl / lib_b / 1e9}
+        print(r, flush=True)
+        res["attention"].append(r)
+    json.dump(res, open("gpurun_out/kbench.json", "w"), indent=1)
+except Exception as e:  # noqa: BLE001
+    print("attention bench failed:", repr(e))
