@@ -63,6 +63,58 @@ SB_DEVICE void load_tile(uint8_t* dst, const CUtensorMap* map, uint64_t* bar, in
   tma_load_2d(dst + kTileBytes / 2, map, bar, col0 + 64, row0);
 }
 
+
+// Softmax inner loops.  The masked variants run only on boundary tiles (diagonal / document edges); keeping the branch
+// outside the unrolled element loops avoids per-element divergence bookkeeping in the common unmasked case.
+template <bool kMask>
+SB_DEVICE float fwd_row_max(uint32_t s_tmem, int kv0, int rs, int re) {
+  float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll 1
+  for (int c = 0; c < BKV; c += 32) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(s_tmem + c, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      float a = __uint_as_float(v[i]), b = __uint_as_float(v[i + 1]), c2 = __uint_as_float(v[i + 2]), d = __uint_as_float(v[i + 3]);
+      if (kMask) {
+        const int key = kv0 + c + i;
+        if (!(key >= rs && key < re)) a = -INFINITY;
+        if (!(key + 1 >= rs && key + 1 < re)) b = -INFINITY;
+        if (!(key + 2 >= rs && key + 2 < re)) c2 = -INFINITY;
+        if (!(key + 3 >= rs && key + 3 < re)) d = -INFINITY;
+      }
+      m0 = fmaxf(m0, a), m1 = fmaxf(m1, b), m2 = fmaxf(m2, c2), m3 = fmaxf(m3, d);
+    }
+  }
+  return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+}
+
+template <bool kMask>
+SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scale_log2, float m_use, float& l0, float& l1) {
+#pragma unroll 1
+  for (int c = 0; c < BKV; c += 32) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(s_tmem + c, v);
+    tmem_ld_wait();
+    uint32_t packed[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float a = exp2f(__uint_as_float(v[2 * i]) * scale_log2 - m_use);
+      float b = exp2f(__uint_as_float(v[2 * i + 1]) * scale_log2 - m_use);
+      if (kMask) {
+        const int key = kv0 + c + 2 * i;
+        if (!(key >= rs && key < re)) a = 0.f;
+        if (!(key + 1 >= rs && key + 1 < re)) b = 0.f;
+      }
+      l0 += a;
+      l1 += b;
+      packed[i] = pack_bf16(a, b);
+    }
+    tmem_st_32x32b_x16(s_tmem + c / 2, packed);
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                      const __grid_constant__ CUtensorMap map_v, const Params p) {
@@ -214,25 +266,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
       const int kv0 = kv_begin + j * BKV;
       mbar_wait(&bars->s_full[x], j & 1);
       tc_fence_after();
-      const bool need_mask = (kv0 < rs) || (kv0 + BKV > re);
+      // warp-uniform so that the warp-collective TMEM loads inside stay convergent
+      const bool need_mask = __any_sync(0xffffffffu, (kv0 < rs) || (kv0 + BKV > re));
       // pass 1: row maximum of the visible scores
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < BKV; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(s_tmem + c, v);
-        tmem_ld_wait();
-        if (need_mask) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int key = kv0 + c + i;
-            if (key >= rs && key < re) mx = fmaxf(mx, __uint_as_float(v[i]));
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-        }
-      }
+      const float mx = need_mask ? fwd_row_max<true>(s_tmem, kv0, rs, re) : fwd_row_max<false>(s_tmem, kv0, rs, re);
       const float m_new = fmaxf(m_ref, mx * p.scale_log2);
       // lazy rescale: keep the old reference unless the max grew by more than 8 (p stays <= 2^8, exact in the end)
       const bool grow = m_new > m_ref + 8.f;
@@ -245,27 +282,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
       const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
       // pass 2: p = exp2(s·scale − m_ref), row sum, bf16 pairs written over the already consumed S columns
       float l0 = 0.f, l1 = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < BKV; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(s_tmem + c, v);
-        tmem_ld_wait();
-        uint32_t packed[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float a = exp2f(__uint_as_float(v[2 * i]) * p.scale_log2 - m_use);
-          float b = exp2f(__uint_as_float(v[2 * i + 1]) * p.scale_log2 - m_use);
-          if (need_mask) {
-            const int key = kv0 + c + 2 * i;
-            if (!(key >= rs && key < re)) a = 0.f;
-            if (!(key + 1 >= rs && key + 1 < re)) b = 0.f;
-          }
-          l0 += a;
-          l1 += b;
-          packed[i] = pack_bf16(a, b);
-        }
-        tmem_st_32x32b_x16(s_tmem + c / 2, packed);
-      }
+      if (need_mask)
+        fwd_exp_pack<true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1);
+      else
+        fwd_exp_pack<false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1);
       l += l0 + l1;
       tmem_st_wait();
       if (j > 0) {
@@ -406,7 +426,9 @@ namespace attn {
 constexpr int BS = 64;                                   // streamed sub-tile rows
 constexpr uint32_t kSubBytes = BS * 128 * 2;             // 16 KiB: [64, 128] bf16 as two 64-column slabs of 8 KiB
 constexpr int kRing = 3;
-constexpr uint32_t kBwdSmemBytes = 2 * kTileBytes + kRing * 2 * kSubBytes + 1024 + 256;
+constexpr int kMaxSubs = 2048;                           // per-sub mask flags (T up to 131072 per packed batch)
+constexpr uint32_t kStatBytes = kRing * 2 * BS * 4;      // staged lse·log2e and delta of the streamed queries
+constexpr uint32_t kBwdSmemBytes = 2 * kTileBytes + kRing * 2 * kSubBytes + kStatBytes + kMaxSubs + 1024 + 256;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct BwdParams {
@@ -415,8 +437,9 @@ struct BwdParams {
   int causal;
   const int* seg_start;
   const int* seg_end;
-  const float* lse;     // [heads, T] natural log
-  const float* delta;   // [heads, T]
+  const float* lse2;    // [heads, Tp] lse · log2(e)   (Tp = padded pitch, multiple of 64 and > T)
+  const float* delta;   // [heads, Tp] Σ_d dO·O
+  int Tp;
   __nv_bfloat16* dq;    // [T, heads, 128]
   __nv_bfloat16* dk;    // [T, kv_heads, 128]
   __nv_bfloat16* dv;
@@ -432,13 +455,21 @@ struct __align__(8) BwdBarriers {
   uint32_t tmem_base;
 };
 
+SB_DEVICE void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 SB_DEVICE void load_sub(uint8_t* dst, const CUtensorMap* map, uint64_t* bar, int col0, int row0) {
   tma_load_2d(dst, map, bar, col0, row0);
   tma_load_2d(dst + kSubBytes / 2, map, bar, col0 + 64, row0);
 }
 
 __global__ void bwd_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
-                                 float* __restrict__ delta, int T, int heads) {
+                                 const float* __restrict__ lse, float* __restrict__ lse2, float* __restrict__ delta, int T,
+                                 int heads, int Tp) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= T * heads) return;
   const int t = w / heads, h = w % heads;
@@ -446,7 +477,10 @@ __global__ void bwd_delta_kernel(const __nv_bfloat16* __restrict__ dout, const _
   const uint2 b = *reinterpret_cast<const uint2*>(out + (size_t)w * 128 + lane * 4);
   float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), b0 = unpack_bf16(b.x), b1 = unpack_bf16(b.y);
   float s = warp_sum(a0.x * b0.x + a0.y * b0.y + a1.x * b1.x + a1.y * b1.y);
-  if (lane == 0) delta[(size_t)h * T + t] = s;
+  if (lane == 0) {
+    delta[(size_t)h * Tp + t] = s;
+    lse2[(size_t)h * Tp + t] = lse[(size_t)h * T + t] * kLog2e;
+  }
 }
 
 SB_DEVICE void store_row_bf16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
@@ -468,6 +502,46 @@ SB_DEVICE void store_row_bf16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
 }
 
 // ------------------------------------------------------------------------------------------------- dK / dV
+
+template <bool kMask>
+SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_lse2, const float* st_del, int qs0, int key,
+                                   bool key_ok, const BwdParams& p) {
+#pragma unroll 1
+  for (int c = 0; c < BS; c += 32) {
+    uint32_t s[32], dp[32];
+    tmem_ld_32x32b_x32(t_s + c, s);
+    tmem_ld_32x32b_x32(t_p + c, dp);
+    tmem_ld_wait();
+    uint32_t pp[16], pd[16];
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+      // four consecutive queries: their lse·log2e and delta come from shared memory as one 16-byte broadcast each
+      const float4 l4 = *reinterpret_cast<const float4*>(st_lse2 + c + 2 * i);
+      const float4 d4 = *reinterpret_cast<const float4*>(st_del + c + 2 * i);
+      const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dl[4] = {d4.x, d4.y, d4.z, d4.w};
+      float pv[4], ds[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float pr = exp2f(__uint_as_float(s[2 * i + e]) * p.scale_log2 - lv[e]);
+        if (kMask) {
+          const int qq = qs0 + c + 2 * i + e;
+          const int qc = min(qq, p.T - 1);
+          const bool vis = key_ok && qq < p.T && key >= __ldg(p.seg_start + qc) &&
+                           key < (p.causal ? qq + 1 : __ldg(p.seg_end + qc));
+          if (!vis) pr = 0.f;
+        }
+        pv[e] = pr;
+        ds[e] = pr * (__uint_as_float(dp[2 * i + e]) - dl[e]) * p.scale;
+      }
+      pp[i] = pack_bf16(pv[0], pv[1]);
+      pp[i + 1] = pack_bf16(pv[2], pv[3]);
+      pd[i] = pack_bf16(ds[0], ds[1]);
+      pd[i + 1] = pack_bf16(ds[2], ds[3]);
+    }
+    tmem_st_32x32b_x16(t_s + c / 2, pp);  // P^T over the consumed S^T columns
+    tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS^T over the consumed dP^T columns
+  }
+}
 __global__ void __launch_bounds__(384, 1)
 attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
                           const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
@@ -477,7 +551,9 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
   uint8_t* sK = smem;
   uint8_t* sV = smem + kTileBytes;
   uint8_t* ring = smem + 2 * kTileBytes;  // stage: [Q_sub | dO_sub]
-  BwdBarriers* bars = reinterpret_cast<BwdBarriers*>(ring + kRing * 2 * kSubBytes);
+  float* stats = reinterpret_cast<float*>(ring + kRing * 2 * kSubBytes);  // stage: [lse2 x 64 | delta x 64]
+  uint8_t* sub_mask = reinterpret_cast<uint8_t*>(stats) + kStatBytes;
+  BwdBarriers* bars = reinterpret_cast<BwdBarriers*>(sub_mask + kMaxSubs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kv0 = blockIdx.x * 128;
@@ -489,6 +565,13 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
   const int q_end = p.seg_end[kv_last];
   const int n_sub = (q_end - q_begin + BS - 1) / BS;
   const int n_it = n_sub * group;
+  // which query sub-tiles need element-wise masking against this key tile (diagonal, document edges, tails)
+  for (int sub = threadIdx.x; sub < n_sub; sub += blockDim.x) {
+    const int qs0 = q_begin + sub * BS;
+    const int q_hi = min(qs0 + BS, p.T) - 1;
+    sub_mask[sub] = (p.causal && qs0 < kv0 + 127) || p.seg_start[q_hi] > kv0 || p.seg_end[min(qs0, p.T - 1)] <= kv_last ||
+                    qs0 + BS > p.T || kv0 + 128 > p.T;
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_q);
@@ -526,9 +609,11 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
         const int head = kvh * group + it / n_sub;
         const int qs0 = q_begin + (it % n_sub) * BS;
         mbar_wait(&bars->ring_empty[st], ((it / kRing) & 1) ^ 1);
-        mbar_arrive_expect_tx(&bars->ring_full[st], 2 * kSubBytes);
+        mbar_arrive_expect_tx(&bars->ring_full[st], 2 * kSubBytes + 2 * BS * 4);
         load_sub(ring + st * 2 * kSubBytes, &map_q, &bars->ring_full[st], head * D, qs0);
         load_sub(ring + st * 2 * kSubBytes + kSubBytes, &map_do, &bars->ring_full[st], head * D, qs0);
+        bulk_load(stats + st * 2 * BS, p.lse2 + (size_t)head * p.Tp + qs0, BS * 4, &bars->ring_full[st]);
+        bulk_load(stats + st * 2 * BS + BS, p.delta + (size_t)head * p.Tp + qs0, BS * 4, &bars->ring_full[st]);
       }
     }
   } else if (warp == 1) {
@@ -584,46 +669,17 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
     const bool key_ok = key < p.T;
     const uint32_t lane_base = (uint32_t)(ew * 32) << 16;
     for (int it = wg; it < n_it; it += 2) {
-      const int head = kvh * group + it / n_sub;
       const int qs0 = q_begin + (it % n_sub) * BS;
-      const float* lse_h = p.lse + (size_t)head * p.T;
-      const float* del_h = p.delta + (size_t)head * p.T;
+      mbar_wait(&bars->ring_full[it % kRing], (it / kRing) & 1);  // makes the staged lse2 / delta visible here
       mbar_wait(&bars->s_full[it & 1], (it >> 1) & 1);
       tc_fence_after();
-      const int q_hi = min(qs0 + BS, p.T) - 1;
-      // fully visible sub-tile: every query sees every key of the tile
-      const bool need_mask = (p.causal && qs0 < kv0 + 127) || p.seg_start[q_hi] > kv0 || p.seg_end[min(qs0, p.T - 1)] <= kv_last ||
-                             qs0 + BS > p.T || kv0 + 128 > p.T;
+      const float* st_lse2 = stats + (it % kRing) * 2 * BS;  // staged by the producer together with Q_sub / dO_sub
+      const float* st_del = st_lse2 + BS;
       const uint32_t t_s = tmem + lane_base + (it & 1) * 128, t_p = t_s + 64;
-#pragma unroll 1
-      for (int c = 0; c < BS; c += 32) {
-        uint32_t s[32], dp[32];
-        tmem_ld_32x32b_x32(t_s + c, s);
-        tmem_ld_32x32b_x32(t_p + c, dp);
-        tmem_ld_wait();
-        uint32_t pp[16], pd[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float pv[2], dv_[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int qq = qs0 + c + 2 * i + e;
-            const int qc = min(qq, p.T - 1);
-            float pr = exp2f(__uint_as_float(s[2 * i + e]) * p.scale_log2 - __ldg(lse_h + qc) * kLog2e);
-            if (need_mask) {
-              const bool vis = key_ok && qq < p.T && key >= __ldg(p.seg_start + qc) &&
-                               key < (p.causal ? qq + 1 : __ldg(p.seg_end + qc));
-              if (!vis) pr = 0.f;
-            }
-            pv[e] = pr;
-            dv_[e] = pr * (__uint_as_float(dp[2 * i + e]) - __ldg(del_h + qc)) * p.scale;
-          }
-          pp[i] = pack_bf16(pv[0], pv[1]);
-          pd[i] = pack_bf16(dv_[0], dv_[1]);
-        }
-        tmem_st_32x32b_x16(t_s + c / 2, pp);   // Pᵀ over the consumed Sᵀ columns
-        tmem_st_32x32b_x16(t_p + c / 2, pd);   // dSᵀ over the consumed dPᵀ columns
-      }
+      if (sub_mask[it % n_sub])
+        dkdv_softmax_chunks<true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p);
+      else
+        dkdv_softmax_chunks<false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -648,6 +704,34 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
 }
 
 // ------------------------------------------------------------------------------------------------- dQ
+
+template <bool kMask>
+SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, int re, float scale_log2, float lse2,
+                                 float del, float scale) {
+#pragma unroll 1
+  for (int c = 0; c < BS; c += 32) {
+    uint32_t s[32], dp[32];
+    tmem_ld_32x32b_x32(t_s + c, s);
+    tmem_ld_32x32b_x32(t_p + c, dp);
+    tmem_ld_wait();
+    uint32_t pd[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float d2[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        float pr = exp2f(__uint_as_float(s[2 * i + e]) * scale_log2 - lse2);
+        if (kMask) {
+          const int kk = ks0 + c + 2 * i + e;
+          if (!(kk >= rs && kk < re)) pr = 0.f;
+        }
+        d2[e] = pr * (__uint_as_float(dp[2 * i + e]) - del) * scale;
+      }
+      pd[i] = pack_bf16(d2[0], d2[1]);
+    }
+    tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS over the consumed dP columns
+  }
+}
 __global__ void __launch_bounds__(384, 1)
 attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
                         const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
@@ -758,38 +842,19 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_
     const int rc = min(row, p.T - 1);
     const int rs = row_ok ? p.seg_start[rc] : 0;
     const int re = row_ok ? (p.causal ? row + 1 : p.seg_end[rc]) : 0;
-    const float lse2 = p.lse[(size_t)head * p.T + rc] * kLog2e;
-    const float del = p.delta[(size_t)head * p.T + rc];
+    const float lse2 = p.lse2[(size_t)head * p.Tp + rc];
+    const float del = p.delta[(size_t)head * p.Tp + rc];
     const uint32_t lane_base = (uint32_t)(ew * 32) << 16;
     for (int it = wg; it < n_it; it += 2) {
       const int ks0 = kv_begin + it * BS;
       mbar_wait(&bars->s_full[it & 1], (it >> 1) & 1);
       tc_fence_after();
-      const bool need_mask = (ks0 < rs) || (ks0 + BS > re);
+      const bool need_mask = __any_sync(0xffffffffu, (ks0 < rs) || (ks0 + BS > re));
       const uint32_t t_s = tmem + lane_base + (it & 1) * 128, t_p = t_s + 64;
-#pragma unroll 1
-      for (int c = 0; c < BS; c += 32) {
-        uint32_t s[32], dp[32];
-        tmem_ld_32x32b_x32(t_s + c, s);
-        tmem_ld_32x32b_x32(t_p + c, dp);
-        tmem_ld_wait();
-        uint32_t pd[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float d2[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            float pr = exp2f(__uint_as_float(s[2 * i + e]) * p.scale_log2 - lse2);
-            if (need_mask) {
-              const int kk = ks0 + c + 2 * i + e;
-              if (!(kk >= rs && kk < re)) pr = 0.f;
-            }
-            d2[e] = pr * (__uint_as_float(dp[2 * i + e]) - del) * p.scale;
-          }
-          pd[i] = pack_bf16(d2[0], d2[1]);
-        }
-        tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS over the consumed dP columns
-      }
+      if (need_mask)
+        dq_softmax_chunks<true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale);
+      else
+        dq_softmax_chunks<false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -831,20 +896,32 @@ static int make_map_box(CUtensorMap* m, const void* ptr, uint64_t width, uint64_
 }  // namespace attn
 }  // namespace sb
 
+// row pitch (floats) of the two per-(head, token) scratch planes: a multiple of 64 with at least 64 slack, so 64-float
+// bulk copies that start at any sub-tile stay in bounds and 16-byte aligned
+extern "C" int sb_attention_bwd_pitch(int T) { return (T + 63) / 64 * 64 + 64; }
+extern "C" long long sb_attention_bwd_scratch_floats(int T, int heads) {
+  return 2ll * heads * sb_attention_bwd_pitch(T);
+}
+
 // dout, out: [T, heads, 128] contiguous; q/k/v as in sb_attention_fwd; lse: [heads, T] from the forward pass;
-// delta: fp32 [heads, T] scratch owned by the caller; dq: [T, heads, 128], dk/dv: [T, kv_heads, 128] contiguous.
+// scratch: fp32 buffer of sb_attention_bwd_scratch_floats(T, heads) owned by the caller (must start zero-filled or at
+// least finite: the padding is read but masked); dq: [T, heads, 128], dk/dv: [T, kv_heads, 128] contiguous.
 extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
-                                const float* lse, float* delta, void* dq, void* dk, void* dv, const int* seg_start,
+                                const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
                                 const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                                 long long v_pitch, float scale, int causal, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
   if (heads % kv_heads) return -1;
+  if ((T + BS - 1) / BS > kMaxSubs) return -3;
+  const int Tp = sb_attention_bwd_pitch(T);
+  float* lse2 = scratch;
+  float* delta = scratch + (size_t)heads * Tp;
   bwd_delta_kernel<<<(T * heads * 32 + 255) / 256, 256, 0, stream>>>((const __nv_bfloat16*)dout, (const __nv_bfloat16*)out,
-                                                                      delta, T, heads);
+                                                                      lse, lse2, delta, T, heads, Tp);
   BwdParams p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale = scale, p.scale_log2 = scale * kLog2e, p.causal = causal;
-  p.seg_start = seg_start, p.seg_end = seg_end, p.lse = lse, p.delta = delta;
+  p.seg_start = seg_start, p.seg_end = seg_end, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
   p.dq = (__nv_bfloat16*)dq, p.dk = (__nv_bfloat16*)dk, p.dv = (__nv_bfloat16*)dv;
   static bool configured = false;
   if (!configured) {

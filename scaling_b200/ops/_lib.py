@@ -46,6 +46,7 @@ _SIGS = {
 _RET_LL = {
     "sb_norm_bwd_scratch_floats": [c_int, c_int, c_int],
     "sb_blend_index": [P, c_int, P, c_longlong],
+    "sb_attention_bwd_scratch_floats": [c_int, c_int],
     "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
 }
 _RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": []}

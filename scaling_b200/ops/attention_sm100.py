@@ -50,7 +50,8 @@ def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, sca
     dq = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     dk = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     dv = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
-    delta = torch.empty((heads, T), dtype=torch.float32, device=q.device)
+    lib = _lib.load(required=True)
+    delta = torch.zeros(lib.sb_attention_bwd_scratch_floats(T, heads), dtype=torch.float32, device=q.device)
     call("sb_attention_bwd", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
          ptr(seg_start), ptr(seg_end), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
          launches=3)
