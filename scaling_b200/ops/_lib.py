@@ -22,6 +22,8 @@ P = c_void_p
 _SIGS = {
     "sb_gemm_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm2_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm2_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_norm_fwd": [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, c_int, P],
     "sb_norm_bwd": [P, P, P, P, P, P, P, P, P, c_int, c_int, P, c_int, c_int, c_int, c_int, P],
     "sb_swiglu_fwd": [P, P, c_int, c_int, P],

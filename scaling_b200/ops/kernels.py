@@ -5,6 +5,7 @@ launches on the current stream.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -13,6 +14,20 @@ from . import _lib
 from ._lib import DTYPE_CODE, call, ptr
 
 _scratch: dict[tuple, torch.Tensor] = {}
+
+# GEMM flavour: "2cta" = CTA pairs (cta_group::2, 256x256 tiles), "1cta" = single-CTA 128x256 tiles
+_GEMM_IMPL = os.environ.get("SCALING_B200_GEMM", "2cta")
+
+
+def set_gemm_impl(name: str) -> None:
+    global _GEMM_IMPL
+    assert name in ("1cta", "2cta")
+    _GEMM_IMPL = name
+
+
+def _gemm_entry(M: int, N: int) -> str:
+    # tiny problems do not fill CTA pairs; keep them on the single-CTA kernel
+    return "sb_gemm2_bf16" if (_GEMM_IMPL == "2cta" and M >= 256 and N >= 128) else "sb_gemm_bf16"
 
 
 def _scratch_buf(device: torch.device, n_floats: int, tag: str) -> torch.Tensor:
@@ -68,7 +83,7 @@ def gemm(
     if bias is not None:
         assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
     call(
-        "sb_gemm_bf16", ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
+        _gemm_entry(M, N), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
         DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
     )
     return out
@@ -85,7 +100,7 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True)
     h = torch.empty((M, F), dtype=torch.bfloat16, device=x.device)
     pre = torch.empty((M, 2 * F), dtype=torch.bfloat16, device=x.device) if keep_pre else None
     call(
-        "sb_gemm_swiglu_bf16", ptr(x), ptr(w_gate_up), ptr(h), ptr(pre), M, F, K, x.stride(0), w_gate_up.stride(0), F,
+        "sb_gemm2_swiglu_bf16" if (_GEMM_IMPL == "2cta" and M >= 256) else "sb_gemm_swiglu_bf16", ptr(x), ptr(w_gate_up), ptr(h), ptr(pre), M, F, K, x.stride(0), w_gate_up.stride(0), F,
         2 * F, 0,
     )
     return h, pre

@@ -7,12 +7,14 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def K():
+@pytest.fixture(scope="module", params=["2cta", "1cta"])
+def K(request):
     from scaling_b200.ops import _lib, kernels
 
     assert _lib.available(), "native library must load on a GPU box"
-    return kernels
+    kernels.set_gemm_impl(request.param)
+    yield kernels
+    kernels.set_gemm_impl("2cta")
 
 
 def _rel_err(a: torch.Tensor, b: torch.Tensor) -> float:

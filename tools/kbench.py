@@ -54,7 +54,9 @@ def bench_gemm(name, M, N, Kd, a_mn=False, b_mn=False, out_dtype=torch.bfloat16,
             "lib_tflops": fl / ref / 1e9, "speedup_vs_lib": ref / ours}
 
 
-res = {"gemm": [], "fused": []}
+import os
+K.set_gemm_impl(os.environ.get("SCALING_B200_GEMM", "2cta"))
+res = {"gemm": [], "fused": [], "gemm_impl": os.environ.get("SCALING_B200_GEMM", "2cta")}
 T = 4096
 shapes = [
     ("qkv_fprop", T, 6144, 4096, False, False, torch.bfloat16, False),
