@@ -8,6 +8,8 @@
 //   leader    : warp 1 issues tcgen05.mma.cta_group::2 and multicast-commits to both CTAs' barriers
 //
 // Same operand layouts and epilogues as gemm_sm100.cu (reference call sites: core/nn/linear/*.py, core/nn/mlp.py).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace sb {
@@ -26,7 +28,24 @@ constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
 constexpr uint32_t kPeerMask = 0xFEFFFFFF;  // clears the CTA-rank bit of a shared::cluster address -> leader's copy
 
-enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2 };
+enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3 };
+
+// ---- fused all-reduce (kAllReduce) ----------------------------------------------------------------------------
+// One launch computes this rank's partial product AND the tensor-parallel sum of it.  Every rank owns a symmetric
+// workspace (peer-mapped over NVLink): per sender a slot of bf16 partial tiles plus one u32 flag per (CTA tile,
+// epilogue warp).  The epilogue warps convert a 32x64 sub-tile at a time, stage it in shared memory and push it with
+// bulk async copies into the slot `tp_rank` of EVERY rank's workspace (its own included), then publish the flag with a
+// system-scope release store once the copies of that tile have completed.  Four extra "reducer" warps per CTA wait for
+// the flags of all senders for the tiles this CTA computed, add the partials in rank order in fp32 (so every rank
+// produces identical bits) and write the bf16 result (+ bias) to D.  The NVLink transfer of tile i overlaps the MMA of
+// tiles i+1.., the reduction of tile i overlaps both.
+constexpr int kMaxTP = 8;
+constexpr int kArThreads = 384;
+constexpr uint32_t kChunkBytes = 32 * 64 * 2;            // one staged sub-tile: 32 rows x 64 bf16
+constexpr uint32_t kSlabBytes = 4 * kChunkBytes;         // one epilogue warp's 32 x 256 slab
+constexpr uint32_t kCtaTileBytes = 4 * kSlabBytes;       // 128 x 256 bf16
+constexpr uint32_t kStagingBytes = 4 * 2 * kChunkBytes;  // 4 warps x double buffer
+constexpr uint32_t kArSmemBytes = kStages * (128 * BK * 2 * 2) + 256 + kStagingBytes + 1024;
 
 struct Params {
   int M, N, K;
@@ -37,6 +56,14 @@ struct Params {
   int ldaux;
   int swiglu_up_row_offset;
   int tiles_m, tiles_n;
+  // kAllReduce only
+  int tp_rank, tp_size;
+  uint32_t epoch;
+  int debug;                      // timing experiments only (SB_AR_DEBUG): 1 no remote data, 2 wait own flags only, 4 no reduce
+  uint32_t flag_slot;             // u32 flags per sender slot
+  unsigned long long slot_bytes;  // bytes per sender slot
+  uint8_t* ar_data[kMaxTP];       // rank r's workspace (this call's parity) as mapped into this process
+  uint32_t* ar_flags[kMaxTP];
 };
 
 struct __align__(8) Barriers {
@@ -45,6 +72,7 @@ struct __align__(8) Barriers {
   uint64_t acc_full[kAccStages];
   uint64_t acc_empty[kAccStages];
   uint32_t tmem_base;
+  uint32_t pushed;  // kAllReduce: epilogue-warp tile pushes completed (4 per CTA tile), read by the signal warp
 };
 
 SB_DEVICE uint32_t cluster_ctarank() {
@@ -101,6 +129,64 @@ SB_DEVICE void tmem_dealloc_2sm(uint32_t taddr) {
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "n"(kCols) : "memory");
 }
 
+SB_DEVICE void bulk_store_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+SB_DEVICE void bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+template <int kN>
+SB_DEVICE void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(kN) : "memory");
+}
+template <int kN>
+SB_DEVICE void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;\n" ::"n"(kN) : "memory");
+}
+SB_DEVICE void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+SB_DEVICE void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+SB_DEVICE void red_release_cta_smem_inc(uint32_t* p) {
+  asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;\n" ::"r"(smem_u32(p)) : "memory");
+}
+SB_DEVICE uint32_t ld_acquire_cta_smem(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];\n" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+SB_DEVICE void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;\n" ::: "memory"); }
+SB_DEVICE uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+SB_DEVICE unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
+// Spin until *flag == epoch.  A peer that never arrives (crashed rank) traps after 30 s instead of hanging the GPU.
+SB_DEVICE void wait_flag(const uint32_t* flag, uint32_t epoch) {
+  if (ld_acquire_sys(flag) == epoch) return;
+  const unsigned long long t0 = global_timer_ns();
+  int spins = 0;
+  while (ld_acquire_sys(flag) != epoch) {
+    if (++spins > 64) {
+      __nanosleep(100);
+      if ((spins & 1023) == 0 && global_timer_ns() - t0 > 30000000000ull) __trap();
+    }
+  }
+}
+SB_DEVICE uint4 ld_cg_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+SB_DEVICE void acc_bf16x8(float* f, const uint4& x) {
+  float2 a = unpack_bf16(x.x), b = unpack_bf16(x.y), c = unpack_bf16(x.z), d = unpack_bf16(x.w);
+  f[0] += a.x, f[1] += a.y, f[2] += b.x, f[3] += b.y, f[4] += c.x, f[5] += c.y, f[6] += d.x, f[7] += d.y;
+}
+
 SB_DEVICE void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
   constexpr int G = 4;
   int per_group = G * tiles_n;
@@ -113,7 +199,7 @@ SB_DEVICE void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
 }
 
 template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kEpi == kAllReduce ? kArThreads : kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -141,6 +227,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       mbar_init(&bars->acc_full[i], 1);
       mbar_init(&bars->acc_empty[i], 8);  // 4 epilogue warps in each of the two CTAs arrive on the leader's barrier
     }
+    bars->pushed = 0;
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc_2sm<512>(&bars->tmem_base);
@@ -222,7 +309,138 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         }
       }
     }
-  } else if (warp >= 4) {
+  } else if (kEpi == kAllReduce && warp == 3) {
+    // ===================== signal warp (kAllReduce): publish "tile pushed" flags off the epilogue's critical path ======
+    if (lane == 0) {
+      uint32_t done = 0;
+      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+        const uint32_t ct = (uint32_t)t * 2 + rank;
+        done += 4;
+        while (ld_acquire_cta_smem(&bars->pushed) < done) __nanosleep(40);
+        fence_acq_rel_sys();  // the four warps' bulk copies (completed, observed through `pushed`) before the flags
+        for (int r = 0; r < p.tp_size; ++r)
+          st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
+      }
+    }
+  } else if (kEpi == kAllReduce && warp >= 8) {
+    // ===================== reducer warps (kAllReduce): sum the senders' partials of this CTA's tiles =====================
+    const int rw = warp - 8;
+    const uint8_t* mine = p.ar_data[p.tp_rank];
+    const uint32_t* myflags = p.ar_flags[p.tp_rank];
+    const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      int tm, tn;
+      tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+      const uint32_t ct = (uint32_t)t * 2 + rank;
+      if (p.debug & 4) continue;
+      if (lane == 0) {
+        for (int s = 0; s < p.tp_size; ++s)
+          if (!(p.debug & 2) || s == p.tp_rank) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
+      }
+      __syncwarp();
+      const uint8_t* base = mine + ((size_t)ct * 4 + rw) * kSlabBytes;
+      const int row0 = tm * BM + rank * 128 + rw * 32;
+      const int n0 = tn * BN;
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint4 xa[8], xb[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const size_t off = (size_t)c4 * kChunkBytes + (size_t)(lane + 32 * it) * 16;
+          xa[it] = ld_cg_v4(base + off);
+          xb[it] = ld_cg_v4(base + p.slot_bytes + off);
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          acc_bf16x8(f, xa[it]);
+          acc_bf16x8(f, xb[it]);
+          const size_t off = (size_t)c4 * kChunkBytes + (size_t)(lane + 32 * it) * 16;
+          for (int s = 2; s < p.tp_size; ++s) acc_bf16x8(f, ld_cg_v4(base + (size_t)s * p.slot_bytes + off));
+          const int r_in = (lane >> 3) + 4 * it;
+          const int j = (lane & 7) ^ (r_in & 7);
+          const int row = row0 + r_in;
+          const int col = n0 + c4 * 64 + j * 8;
+          if (row >= p.M || col >= p.N) continue;
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd + col;
+          if (col + 8 <= p.N) {
+            if (bias) {
+              const uint4 bv = *reinterpret_cast<const uint4*>(bias + col);
+              acc_bf16x8(f, bv);
+            }
+            *reinterpret_cast<uint4*>(dst) =
+                make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+          } else {
+            for (int i = 0; i < 8 && col + i < p.N; ++i)
+              dst[i] = __float2bfloat16(f[i] + (bias ? __bfloat162float(bias[col + i]) : 0.f));
+          }
+        }
+      }
+    }
+  } else if (kEpi == kAllReduce && warp >= 4) {
+    // ===================== epilogue (kAllReduce): push bf16 partial tiles into every rank's workspace =====================
+    const int ew = warp & 3;
+    uint8_t* staging = smem + kStages * kStageBytes + 256 + (uint32_t)ew * 2 * kChunkBytes;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int pending_ct = -1;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      const uint32_t ct = (uint32_t)t * 2 + rank;
+      mbar_wait(&bars->acc_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
+      const size_t slab_off = (size_t)p.tp_rank * p.slot_bytes + ((size_t)ct * 4 + ew) * kSlabBytes;
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint8_t* buf = staging + (c4 & 1) * kChunkBytes;
+        if (lane == 0) bulk_wait_read<1>();  // the copies that last read this buffer have drained it
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c4 * 64 + h * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 o = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                                       pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                                       pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                                       pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
+            const int pos = (h * 4 + i) ^ (lane & 7);  // 16-byte unit swizzle: conflict-free staging stores
+            *reinterpret_cast<uint4*>(buf + lane * 128 + pos * 16) = o;
+          }
+        }
+        if (c4 == 3) {  // accumulator fully read: hand the TMEM stage back before the pushes
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          for (int r = 0; r < p.tp_size; ++r)
+            if (!(p.debug & 1) || r == p.tp_rank)
+              bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
+          bulk_commit();
+        }
+      }
+      if (lane == 0) {
+        if (pending_ct >= 0) {  // the previous tile's four groups have completed: hand it to the signal warp
+          bulk_wait<4>();
+          red_release_cta_smem_inc(&bars->pushed);
+        }
+        pending_ct = (int)ct;
+      }
+      if (++acc == kAccStages) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (lane == 0 && pending_ct >= 0) {
+      bulk_wait<0>();
+      red_release_cta_smem_inc(&bars->pushed);
+    }
+  } else if (kEpi != kAllReduce && warp >= 4) {
     // ===================== epilogue (both CTAs, own 128 rows) =====================
     const int ew = warp & 3;
     int acc = 0;
@@ -395,14 +613,18 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
   static bool configured = false;
   if (!configured) {
-    SB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    SB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(EPI == kAllReduce ? kArSmemBytes : kSmemBytes)));
     configured = true;
   }
   int tiles = p.tiles_m * p.tiles_n;
   int clusters = num_sms() / 2;
   if (tiles < clusters) clusters = tiles;
   if (max_ctas > 0 && clusters > max_ctas / 2) clusters = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
-  kern<<<clusters * 2, kThreads, kSmemBytes, stream>>>(ta, tb, p);
+  if (EPI == kAllReduce)
+    kern<<<clusters * 2, kArThreads, kArSmemBytes, stream>>>(ta, tb, p);
+  else
+    kern<<<clusters * 2, kThreads, kSmemBytes, stream>>>(ta, tb, p);
   return (int)cudaGetLastError();
 }
 
@@ -459,4 +681,57 @@ extern "C" int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void*
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (F + BN / 2 - 1) / (BN / 2);
   return launch<0, 0, kSwiGLU, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
+}
+
+// Fused tensor-parallel GEMM + all-reduce: D = sum over ranks of op(A)·op(B) (+ bias), bf16, identical bits on every
+// rank.  `data_ptrs[r]` / `flag_ptrs[r]` are rank r's symmetric workspace regions (for this call's parity) as mapped
+// into this process; `epoch` must be unique per call on a workspace parity and equal on all ranks.  Replaces the
+// reference's GEMM followed by torch.distributed.all_reduce (core/nn/linear/row_parallel_linear.py:150-160, and the
+// backward all-reduce of core/nn/linear/utils.py copy_to_tensor_model_parallel_region).
+extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
+                                       int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
+                                       const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                                       unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas,
+                                       cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if (tp_size < 2 || tp_size > kMaxTP || tp_rank < 0 || tp_rank >= tp_size) return -20;
+  CUtensorMap ta, tb;
+  int rc;
+  if (a_layout == 0)
+    rc = make_map_2d(&ta, A, K, M, lda, BK, 128);
+  else
+    rc = make_map_2d(&ta, A, M, K, lda, 64, BK);
+  if (rc) return 1000 + rc;
+  if (b_layout == 0)
+    rc = make_map_2d(&tb, B, K, N, ldb, BK, 128);
+  else
+    rc = make_map_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return 2000 + rc;
+  Params p{};
+  p.M = M, p.N = N, p.K = K, p.D = D, p.ldd = ldd, p.bias = bias;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + BN - 1) / BN;
+  const unsigned long long cta_tiles = 2ull * p.tiles_m * p.tiles_n;
+  if (cta_tiles * kCtaTileBytes > slot_bytes || cta_tiles > flag_slot) return -21;
+  {
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("SB_AR_DEBUG");
+      dbg = e ? atoi(e) : 0;
+    }
+    p.debug = dbg;
+  }
+  p.tp_rank = tp_rank, p.tp_size = tp_size, p.epoch = epoch, p.flag_slot = flag_slot, p.slot_bytes = slot_bytes;
+  for (int r = 0; r < tp_size; ++r) {
+    p.ar_data[r] = reinterpret_cast<uint8_t*>(data_ptrs[r]);
+    p.ar_flags[r] = reinterpret_cast<uint32_t*>(flag_ptrs[r]);
+  }
+  if (a_layout == 0 && b_layout == 0) return launch<0, 0, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
+  if (a_layout == 0 && b_layout == 1) return launch<0, 1, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
+  return -10;
+}
+
+// Bytes of workspace one sender slot needs for an [M, N] fused all-reduce, and flags per slot.
+extern "C" long long sb_gemm2_allreduce_slot_bytes(int M, int N) {
+  return 2ll * ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (long long)kCtaTileBytes;
 }

@@ -24,6 +24,7 @@ import torch
 from ...ops import functional as OF
 from ...ops.attention import attention as attention_op
 from ...ops.attention import dense_mask, repeat_kv  # noqa: F401  (re-exported helpers)
+from ...parallel.symm import get_tp_comm
 from ..topology import Topology
 from .linear import ColumnParallelLinear, RowParallelLinear
 from .lora import LoRaConfig, LoRAModuleType, ParallelLoRa
@@ -180,9 +181,13 @@ class ParallelSelfAttention(torch.nn.Module):
         if self.qkv_in_one:
             qkv = self.query_key_value(x).view(T, nh, 3 * d)
             return qkv[..., :d], qkv[..., d:2 * d], qkv[..., 2 * d:]
+        comm = get_tp_comm(self.topology) if x.is_cuda else None
+        biases = (self.query.get_bias(), self.key.get_bias(), self.value.get_bias())
+        if comm is not None and all(bb is None for bb in biases):  # dX all-reduce inside the fused dgrad GEMM
+            q, k, v = OF.multi_linear(x, (self.query.weight, self.key.weight, self.value.weight), comm=comm)
+            return q.reshape(T, nh, d), k.reshape(T, nkv, d), v.reshape(T, nkv, d)
         if not self._sp():
             x = copy_to_tensor_model_parallel_region(x, self.topology)
-        biases = (self.query.get_bias(), self.key.get_bias(), self.value.get_bias())
         if all(bb is None for bb in biases):
             q, k, v = OF.multi_linear(x, (self.query.weight, self.key.weight, self.value.weight))
         else:
@@ -257,14 +262,13 @@ class ParallelSelfAttention(torch.nn.Module):
             ctx = attention_op(q, k, v, window=window, **common)
         ctx = ctx.reshape(b, s, nh * d)
 
-        out = self.dense(ctx)  # partial sum over this rank's heads
         if self._sp():
-            out = all_reduce_scatter_to_sequence_parallel(out, self.topology)
+            out = all_reduce_scatter_to_sequence_parallel(self.dense(ctx), self.topology)
+            bias = self.dense.get_bias()
+            if bias is not None:
+                out = out + bias
         else:
-            out = all_reduce(out, self.topology)
-        bias = self.dense.get_bias()
-        if bias is not None:
-            out = out + bias
+            out = self.dense(ctx, reduce=True)  # Σ over the ranks' heads (+ bias once), fused into the GEMM launch
         if self.lora_config and not self.lora_merged_state and LoRAModuleType.DENSE in self.lora_config.parallel_modules:
             full = all_concat(ctx, dim=-1, topology=self.topology)
             lora_out = self.lora_modules[f"dense_{self.lora_config.name}"](full)

@@ -13,6 +13,7 @@ from typing import Callable, List, Optional
 import torch
 
 from ...ops import functional as OF
+from ...parallel.symm import get_tp_comm
 from ..topology import Topology
 from .parameter_meta import CoreParameterMeta
 from .tp_ops import (
@@ -64,9 +65,13 @@ class ColumnParallelLinear(torch.nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         sp = self.topology is not None and self.topology.config.sequence_parallel
-        if not sp:  # under SP the gather in front already turns the gradient into a reduce-scatter
-            x = copy_to_tensor_model_parallel_region(x, self.topology)
-        y = OF.linear(x, self.weight, self.get_bias())
+        comm = get_tp_comm(self.topology) if x.is_cuda else None
+        if comm is not None:  # dX all-reduce runs inside the dgrad GEMM launch
+            y = OF.linear(x, self.weight, self.get_bias(), comm=comm, reduce_input_grad=True)
+        else:
+            if not sp:  # under SP the gather in front already turns the gradient into a reduce-scatter
+                x = copy_to_tensor_model_parallel_region(x, self.topology)
+            y = OF.linear(x, self.weight, self.get_bias())
         if not self.parallel_output:
             y = all_concat(y, dim=-1, topology=self.topology)
         return y
@@ -103,19 +108,21 @@ class RowParallelLinear(torch.nn.Module):
     def get_bias(self) -> Optional[torch.Tensor]:
         return None if self.bias_name is None else getattr(self, self.bias_name)
 
-    def forward(self, x: torch.Tensor, skip_bias_add: bool = False) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, skip_bias_add: bool = False, reduce: bool = False) -> torch.Tensor:
         """``parallel_output=True`` returns this rank's partial sum (the caller reduces, e.g. reduce-scatter under
-        SP) and never adds the bias; ``skip_bias_add`` lets the caller fuse bias + dropout + residual."""
+        SP) and never adds the bias — unless ``reduce`` asks for the all-reduced, biased result anyway (callers
+        that know they are not sequence parallel; the reduction then runs inside the GEMM launch over NVLink peer
+        memory when a TPComm exists).  ``skip_bias_add`` lets the caller fuse bias + dropout + residual."""
         if not self.parallel_input:
             x = all_shard(x, dim=-1, topology=self.topology)
-        y = OF.linear(x, self.weight, None)
-        if self.parallel_output:
-            return y
-        y = all_reduce(y, self.topology)
-        b = self.get_bias()
-        if b is not None and not skip_bias_add:
-            y = y + b
-        return y
+        if self.parallel_output and not reduce:
+            return OF.linear(x, self.weight, None)
+        b = None if skip_bias_add else self.get_bias()
+        comm = get_tp_comm(self.topology) if x.is_cuda else None
+        if comm is not None:
+            return OF.linear(x, self.weight, b, comm=comm, reduce_output=True)
+        y = all_reduce(OF.linear(x, self.weight, None), self.topology)
+        return y if b is None else y + b
 
 
 class VocabParallelEmbedding(torch.nn.Module):

@@ -11,10 +11,11 @@ from typing import Callable, Optional
 import torch
 
 from ...ops import functional as OF
+from ...parallel.symm import get_tp_comm
 from ..topology import Topology
 from .activation import ActivationFunction, get_activation_function
 from .linear import ColumnParallelLinear, RowParallelLinear
-from .tp_ops import all_reduce, all_reduce_scatter_to_sequence_parallel, copy_to_tensor_model_parallel_region
+from .tp_ops import all_reduce_scatter_to_sequence_parallel, copy_to_tensor_model_parallel_region
 
 InitFn = Callable[[torch.Tensor], torch.Tensor]
 
@@ -29,12 +30,12 @@ def _sp(topology: Optional[Topology]) -> bool:
     return topology is not None and topology.config.sequence_parallel
 
 
-def _finish_row_parallel(y: torch.Tensor, layer: RowParallelLinear, topology: Optional[Topology]) -> torch.Tensor:
-    """Reduce a row-parallel partial sum (reduce-scatter under SP, all-reduce otherwise), then add the bias once."""
-    if _sp(topology):
-        y = all_reduce_scatter_to_sequence_parallel(y, topology)
-    else:
-        y = all_reduce(y, topology)
+def _row_parallel_out(layer: RowParallelLinear, h: torch.Tensor, topology: Optional[Topology]) -> torch.Tensor:
+    """Row-parallel projection with its reduction (reduce-scatter under SP; otherwise the all-reduce, fused into the
+    GEMM launch when the TP group has a peer-memory communicator) and the bias added once."""
+    if not _sp(topology):
+        return layer(h, reduce=True)
+    y = all_reduce_scatter_to_sequence_parallel(layer(h), topology)
     b = layer.get_bias()
     return y if b is None else y + b
 
@@ -60,7 +61,7 @@ class ParallelMLP(torch.nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         h = self.activation_function(self.dense_in(x))
-        return _finish_row_parallel(self.dense_out(h), self.dense_out, self.topology)
+        return _row_parallel_out(self.dense_out, h, self.topology)
 
 
 class ParallelSwiGLUMLP(torch.nn.Module):
@@ -80,11 +81,14 @@ class ParallelSwiGLUMLP(torch.nn.Module):
         self.dense_out = RowParallelLinear(f, io_features, parallel_input=True, parallel_output=True, **kw)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if not _sp(self.topology):
+        comm = get_tp_comm(self.topology) if x.is_cuda else None
+        if comm is None and not _sp(self.topology):
             x = copy_to_tensor_model_parallel_region(x, self.topology)  # one dX all-reduce for gate and up together
         bg, bu = self.dense_in.get_bias(), self.siglu_weight.get_bias()
         if bg is None and bu is None:
-            h = OF.swiglu_linear(x, self.dense_in.weight, self.siglu_weight.weight)
+            h = OF.swiglu_linear(x, self.dense_in.weight, self.siglu_weight.weight, comm=comm)
         else:
+            if comm is not None:
+                x = OF._CopyToRegion.apply(x, comm)
             h = torch.nn.functional.silu(OF.linear(x, self.dense_in.weight, bg)) * OF.linear(x, self.siglu_weight.weight, bu)
-        return _finish_row_parallel(self.dense_out(h), self.dense_out, self.topology)
+        return _row_parallel_out(self.dense_out, h, self.topology)

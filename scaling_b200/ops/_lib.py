@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_float, c_int, c_longlong, c_ulonglong, c_void_p
+from ctypes import c_float, c_int, c_longlong, c_uint, c_ulonglong, c_void_p
 from pathlib import Path
 from typing import Optional
 
@@ -24,6 +24,8 @@ _SIGS = {
     "sb_gemm_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm2_allreduce_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int,
+                                c_uint, c_ulonglong, c_uint, c_int, P],
     "sb_norm_fwd": [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, c_int, P],
     "sb_norm_bwd": [P, P, P, P, P, P, P, P, P, c_int, c_int, P, c_int, c_int, c_int, c_int, P],
     "sb_swiglu_fwd": [P, P, c_int, c_int, P],
@@ -50,6 +52,7 @@ _RET_LL = {
     "sb_blend_index": [P, c_int, P, c_longlong],
     "sb_attention_bwd_scratch_floats": [c_int, c_int],
     "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
+    "sb_gemm2_allreduce_slot_bytes": [c_int, c_int],
 }
 _RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": []}
 

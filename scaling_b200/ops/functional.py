@@ -55,6 +55,47 @@ def _gemm_nn(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     return K.gemm(dy, w, b_mn=True)
 
 
+# ---- tensor-parallel reductions fused into the GEMM (scaling_b200.parallel.TPComm) --------------------------------
+def _fusable(m: int, n: int) -> bool:
+    return m >= 256 and n >= 128
+
+
+def _gemm_nt_reduce(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], comm) -> torch.Tensor:
+    """Σ_tp x_r·w_rᵀ (+ bias once): one fused launch, or GEMM + NCCL all-reduce for shapes below the 2-CTA tile."""
+    if _fusable(x.shape[0], w.shape[0]):
+        return K.gemm_allreduce(x, w, comm, bias=bias)
+    y = _gemm_nt(x, w)
+    comm.all_reduce_(y)
+    return y if bias is None else y.add_(bias)
+
+
+def _gemm_nn_reduce(dy: torch.Tensor, w: torch.Tensor, comm) -> torch.Tensor:
+    if _fusable(dy.shape[0], w.shape[1]):
+        return K.gemm_allreduce(dy, w, comm, b_mn=True)
+    return comm.all_reduce_(_gemm_nn(dy, w))
+
+
+class _CopyToRegion(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, comm):
+        ctx.comm = comm
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        return ctx.comm.all_reduce_(g.contiguous()), None
+
+
+class _ReduceFromRegion(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, comm):
+        return comm.all_reduce_(x.contiguous().clone())
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None
+
+
 def _accumulate_wgrad(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> Optional[torch.Tensor]:
     """dW = dyᵀ·x. Into ``weight.main_grad`` (returns None) or as a fresh tensor."""
     main = getattr(weight, "main_grad", None)
@@ -68,12 +109,16 @@ def _accumulate_wgrad(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -
 
 class _LinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, comm=None, reduce_output=False, reduce_input_grad=False):
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
         if not x2.is_contiguous():
             x2 = x2.contiguous()
-        y = _gemm_nt(x2, weight, bias)
+        if comm is not None and reduce_output:
+            y = _gemm_nt_reduce(x2, weight, bias, comm)
+        else:
+            y = _gemm_nt(x2, weight, bias)
+        ctx.comm = comm if reduce_input_grad else None
         ctx.save_for_backward(x2, weight)
         ctx.has_bias = bias is not None
         ctx.x_shape = shape
@@ -87,21 +132,34 @@ class _LinearFn(torch.autograd.Function):
             dy2 = dy2.contiguous()
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = _gemm_nn(dy2, weight).view(ctx.x_shape)
+            dx = (_gemm_nn_reduce(dy2, weight, ctx.comm) if ctx.comm is not None else _gemm_nn(dy2, weight))
+            dx = dx.view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             dw = _accumulate_wgrad(dy2, x2, weight)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.sum(0)
-        return dx, dw, db
+        return dx, dw, db, None, None, None
 
 
-def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """y = x·Wᵀ (+ b) — replaces F.linear in Column/RowParallelLinear (reference column_parallel_linear.py:151)."""
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, *, comm=None,
+           reduce_output: bool = False, reduce_input_grad: bool = False) -> torch.Tensor:
+    """y = x·Wᵀ (+ b) — replaces F.linear in Column/RowParallelLinear (reference column_parallel_linear.py:151).
+
+    With a :class:`~scaling_b200.parallel.TPComm`: ``reduce_output`` sums y over the TP group (row-parallel forward;
+    the bias is added once, after the sum) and ``reduce_input_grad`` sums dX over it (column-parallel backward) —
+    each inside the GEMM launch that produces the operand, instead of an NCCL all-reduce behind it."""
     if (native_enabled(x) and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
             and _aligned(weight.shape[0], weight.shape[1]) and x.numel() > 0
             and (bias is None or bias.dtype == torch.bfloat16)):
-        return _LinearFn.apply(x, weight, bias)
-    return F.linear(x, weight, bias)
+        return _LinearFn.apply(x, weight, bias, comm, reduce_output, reduce_input_grad)
+    if comm is None:
+        return F.linear(x, weight, bias)
+    if reduce_input_grad:
+        x = _CopyToRegion.apply(x, comm)
+    if not reduce_output:
+        return F.linear(x, weight, bias)
+    y = _ReduceFromRegion.apply(F.linear(x, weight, None), comm)
+    return y if bias is None else y + bias
 
 
 # ------------------------------------------------------------------------------------------------ fused q|k|v etc.
@@ -115,13 +173,14 @@ class _MultiLinearFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, fused_w, fused_main_grad, *weights):
+    def forward(ctx, x, fused_w, fused_main_grad, comm, *weights):
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
         if not x2.is_contiguous():
             x2 = x2.contiguous()
         y = _gemm_nt(x2, fused_w)
         ctx.save_for_backward(x2, fused_w)
+        ctx.comm = comm
         ctx.fused_main_grad = fused_main_grad
         ctx.sizes = [w.shape[0] for w in weights]
         ctx.x_shape = shape
@@ -133,16 +192,19 @@ class _MultiLinearFn(torch.autograd.Function):
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dx = _gemm_nn(dy2, fused_w).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = _gemm_nn_reduce(dy2, fused_w, ctx.comm) if ctx.comm is not None else _gemm_nn(dy2, fused_w)
+            dx = dx.view(ctx.x_shape)
         grads: list = [None] * len(ctx.sizes)
-        if not any(ctx.needs_input_grad[3:]):
+        if not any(ctx.needs_input_grad[4:]):
             pass  # frozen weights: no wgrad GEMM at all
         elif ctx.fused_main_grad is not None:
             K.gemm(dy2, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
         else:
             dw = K.gemm(dy2, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
             grads = list(dw.split(ctx.sizes, dim=0))
-        return (dx, None, None, *grads)
+        return (dx, None, None, None, *grads)
 
 
 def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
@@ -165,16 +227,19 @@ def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
         return None
 
 
-def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...]) -> Tuple[torch.Tensor, ...]:
-    """(x·W_0ᵀ, x·W_1ᵀ, …) — one GEMM when the weights are adjacent in the arena, separate linears otherwise."""
+def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None) -> Tuple[torch.Tensor, ...]:
+    """(x·W_0ᵀ, x·W_1ᵀ, …) — one GEMM when the weights are adjacent in the arena, separate linears otherwise.
+    ``comm``: sum dX over the TP group inside the dgrad GEMM (column-parallel projections of a replicated input)."""
     if native_enabled(x) and x.dtype == torch.bfloat16 and all(_aligned(*w.shape) for w in weights) and x.numel() > 0:
         fw = fused_view(tuple(w.data for w in weights))
         if fw is not None:
             mains = [getattr(w, "main_grad", None) for w in weights]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                y = _MultiLinearFn.apply(x, fw, fmg, *weights)
+                y = _MultiLinearFn.apply(x, fw, fmg, comm, *weights)
                 return tuple(y.split([w.shape[0] for w in weights], dim=-1))
+    if comm is not None:
+        x = _CopyToRegion.apply(x, comm)
     return tuple(linear(x, w) for w in weights)
 
 
@@ -185,7 +250,8 @@ class _SwiGLUFn(torch.autograd.Function):
     element-wise pass and runs one dgrad + one wgrad GEMM over the concatenated [2F, K] weight."""
 
     @staticmethod
-    def forward(ctx, x, fused_w, fused_main_grad, w_gate, w_up):
+    def forward(ctx, x, fused_w, fused_main_grad, comm, w_gate, w_up):
+        ctx.comm = comm
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
         if not x2.is_contiguous():
@@ -203,19 +269,22 @@ class _SwiGLUFn(torch.autograd.Function):
         if not dh2.is_contiguous():
             dh2 = dh2.contiguous()
         dpre, _ = K.swiglu_bwd(pre, dh2)
-        dx = _gemm_nn(dpre, fused_w).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = _gemm_nn_reduce(dpre, fused_w, ctx.comm) if ctx.comm is not None else _gemm_nn(dpre, fused_w)
+            dx = dx.view(ctx.x_shape)
         dg = du = None
-        if not any(ctx.needs_input_grad[3:]):
+        if not any(ctx.needs_input_grad[4:]):
             pass
         elif ctx.fused_main_grad is not None:
             K.gemm(dpre, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
         else:
             dw = K.gemm(dpre, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
             dg, du = dw.split(dw.shape[0] // 2, dim=0)
-        return dx, None, None, dg, du
+        return dx, None, None, None, dg, du
 
 
-def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Parameter) -> torch.Tensor:
+def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Parameter, comm=None) -> torch.Tensor:
     if (native_enabled(x) and x.dtype == torch.bfloat16 and _aligned(*w_gate.shape) and w_gate.shape == w_up.shape
             and x.numel() > 0):
         fw = fused_view((w_gate.data, w_up.data))
@@ -223,7 +292,9 @@ def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Pa
             mains = [getattr(w_gate, "main_grad", None), getattr(w_up, "main_grad", None)]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                return _SwiGLUFn.apply(x, fw, fmg, w_gate, w_up)
+                return _SwiGLUFn.apply(x, fw, fmg, comm, w_gate, w_up)
+    if comm is not None:
+        x = _CopyToRegion.apply(x, comm)
     return F.silu(linear(x, w_gate)) * linear(x, w_up)
 
 

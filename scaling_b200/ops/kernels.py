@@ -89,6 +89,35 @@ def gemm(
     return out
 
 
+def gemm_allreduce(a: torch.Tensor, b: torch.Tensor, comm, *, b_mn: bool = False, bias: Optional[torch.Tensor] = None,
+                   out: Optional[torch.Tensor] = None, max_ctas: int = 0) -> torch.Tensor:
+    """D[M,N] = Σ_ranks A_r · B_rᵀ (+ bias) in ONE launch: the tcgen05 GEMM pushes its partial tiles over NVLink into
+    every TP rank's symmetric workspace while later tiles are still in the tensor cores, and reducer warps of the
+    same kernel sum them (``comm`` is a :class:`scaling_b200.parallel.TPComm`).  Bit-identical on all ranks."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, f"inner dimensions differ: {K} vs {Kb}"
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype == torch.bfloat16
+    lda, ldb, ldd = a.stride(0), b.stride(0), out.stride(0)
+    assert gemm_supported(M, N, K, lda, ldb, ldd), "leading dimensions must be multiples of 8 elements"
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    comm.reserve(M, N)
+    epoch, data_ptrs, flag_ptrs = comm.next_call()
+    call(
+        "sb_gemm2_allreduce_bf16", ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, 0, int(b_mn),
+        data_ptrs, flag_ptrs, comm.rank, comm.size, epoch, comm.slot_bytes, comm.flag_slot, max_ctas,
+    )
+    return out
+
+
 def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """h = silu(x·W1ᵀ) ⊙ (x·W2ᵀ) with ``w_gate_up`` = [W1; W2] ([2F, K]); returns (h [M,F], pre [M,2F] or None)."""
     assert x.dtype == torch.bfloat16 and w_gate_up.dtype == torch.bfloat16

