@@ -40,6 +40,7 @@ def parse_args() -> argparse.Namespace:
     p.add_argument("--ops", choices=["sm100", "torch"], default="sm100")
     p.add_argument("--act-ckpt", choices=["disabled", "every_layer", "every_pipe_stage"], default="disabled")
     p.add_argument("--seqs-per-gpu", type=int, default=SEQS_PER_GPU)
+    p.add_argument("--layout", default=None, help="development: tp,pp,dp override of the headline layout")
     return p.parse_args()
 
 
@@ -276,7 +277,7 @@ def result_line(args, n, impl, ms_total, clocks, extra: dict) -> dict:
         },
     }
     line.update(extra)
-    if args.layers != 32 or args.seqs_per_gpu != SEQS_PER_GPU:
+    if args.layers != 32 or args.seqs_per_gpu != SEQS_PER_GPU or args.layout:
         line["non_headline"] = "development knobs changed the model/batch; not the BASELINE config"
     return line
 
@@ -297,6 +298,15 @@ def run_reference(args: argparse.Namespace) -> None:
     os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
     try:
         import torch
+        import torch.utils._pytree as _pytree
+
+        # Environment shim, outside the reference tree: the reference targets torch 2.1, where pytree TreeSpec objects
+        # were mutable; its pipeline communicator assigns `spec.num_leaves` (communicator.py:186).  torch 2.11 froze
+        # the dataclass, so give it back a plain __setattr__.  The reference source itself stays unmodified.
+        if getattr(getattr(_pytree.TreeSpec, "__dataclass_params__", None), "frozen", False):
+            for _cls in [_pytree.TreeSpec, *_pytree.TreeSpec.__subclasses__()]:  # LeafSpec has its own frozen setter
+                if "__setattr__" in _cls.__dict__:
+                    _cls.__setattr__ = lambda self, k, v: object.__setattr__(self, k, v)  # type: ignore
         from scaling.core import Topology  # type: ignore
         from scaling.core.logging import logger  # type: ignore
         from scaling.core.runner import LaunchConfig  # type: ignore
@@ -345,9 +355,12 @@ def run_reference(args: argparse.Namespace) -> None:
         import traceback
 
         traceback.print_exc()
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:240]}"}))
-        return
+        print(json.dumps({"impl": "reference", "rank": rank,
+                          "unavailable": f"{type(e).__name__}: {str(e)[:240]}"}), flush=True)
+        sys.stderr.flush()
+        # peers may be blocked in a collective with this rank: leave without the final barrier so the launcher
+        # tears the job down instead of hanging
+        os._exit(0 if world == 1 else 1)
     if rank == 0:
         tokens_per_s = gb * SEQ * args.steps / (ms / 1e3)
         # the reference's step always loads its batch from the host loader and returns the loss to the host,
@@ -374,6 +387,10 @@ def run_ours(args: argparse.Namespace) -> None:
 def main() -> None:
     args = parse_args()
     assert args.gpus in LAYOUTS, f"--gpus must be one of {sorted(LAYOUTS)}"
+    if args.layout:
+        tp, pp, dp = (int(v) for v in args.layout.split(","))
+        assert tp * pp * dp == args.gpus
+        LAYOUTS[args.gpus] = (tp, pp, dp)
     if args.impl == "reference":
         run_reference(args)
     else:

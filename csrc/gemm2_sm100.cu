@@ -8,6 +8,7 @@
 //   leader    : warp 1 issues tcgen05.mma.cta_group::2 and multicast-commits to both CTAs' barriers
 //
 // Same operand layouts and epilogues as gemm_sm100.cu (reference call sites: core/nn/linear/*.py, core/nn/mlp.py).
+#include <cstdio>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -596,6 +597,9 @@ static int make_map_2d(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    fprintf(stderr, "[scaling_b200] cuTensorMapEncodeTiled failed: CUresult=%d ptr=%p inner=%llu outer=%llu ld=%llu box=%ux%u\n",
+            (int)r, ptr, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner, box_outer);
   return r == CUDA_SUCCESS ? 0 : -2;
 }
 static int num_sms() {

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import threading
 from ctypes import c_float, c_int, c_longlong, c_uint, c_ulonglong, c_void_p
 from pathlib import Path
 from typing import Optional
@@ -16,6 +17,7 @@ import torch
 
 _LIB_PATH = Path(__file__).resolve().parents[1] / "_kernels.so"
 _lib: Optional[ctypes.CDLL] = None
+_tls = threading.local()  # per-thread: which device's context this thread has been bound to
 _launches = 0  # number of kernel launches issued through this binding (bench.py reports it as gpu_launches)
 
 P = c_void_p
@@ -54,7 +56,7 @@ _RET_LL = {
     "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
     "sb_gemm2_allreduce_slot_bytes": [c_int, c_int],
 }
-_RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": []}
+_RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int]}
 
 
 def lib_path() -> Path:
@@ -128,6 +130,12 @@ def call(name: str, *args, launches: int = 1) -> None:
     """Invoke a kernel entry point on the current stream and raise on a non-zero status."""
     global _launches
     lib = load(required=True)
+    dev = torch.cuda.current_device()
+    if getattr(_tls, "device", -1) != dev:  # e.g. an autograd worker thread making its first native call
+        rc = lib.sb_bind_device(dev)
+        if rc != 0:
+            raise RuntimeError(f"sb_bind_device({dev}) failed with CUDA error {rc}")
+        _tls.device = dev
     rc = getattr(lib, name)(*args, stream())
     if rc != 0:
         raise RuntimeError(f"{name} failed with status {rc}")

@@ -82,10 +82,16 @@ def gemm(
     assert gemm_supported(M, N, K, lda, ldb, ldd), "leading dimensions must be multiples of 8 elements"
     if bias is not None:
         assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
-    call(
-        _gemm_entry(M, N), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
-        DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
-    )
+    try:
+        call(
+            _gemm_entry(M, N), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
+            DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
+        )
+    except RuntimeError as e:
+        raise RuntimeError(
+            f"{e}: M={M} N={N} K={K} a={tuple(a.shape)}/{a.stride()}@{a.data_ptr():#x} "
+            f"b={tuple(b.shape)}/{b.stride()}@{b.data_ptr():#x} out={tuple(out.shape)}/{out.stride()}@{out.data_ptr():#x} "
+            f"a_mn={a_mn} b_mn={b_mn} acc={accumulate}") from e
     return out
 
 
