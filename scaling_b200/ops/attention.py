@@ -51,7 +51,7 @@ def dense_mask(cu_q: torch.Tensor, tq: int, cu_k: torch.Tensor, tk: int, causal:
     pos_q = torch.arange(tq, device=cu_q.device) - cu_q64[seg_q.clamp(max=len(cu_q) - 2)]
     pos_k = torch.arange(tk, device=cu_k.device) - cu_k64[seg_k.clamp(max=len(cu_k) - 2)]
     len_q = (cu_q64[1:] - cu_q64[:-1])[seg_q.clamp(max=len(cu_q) - 2)]
-    len_k = (cu_k64[1:] - cu_k64[:-1])[seg_k.clamp(max=len(cu_k) - 2)]
+    len_k = (cu_k64[1:] - cu_k64[:-1])[seg_q.clamp(max=len(cu_k) - 2)]  # key length of each QUERY's sequence
     pos_q = pos_q + (len_k - len_q)  # right-align
     mask = seg_q[:, None] != seg_k[None, :]
     if causal:
