@@ -92,7 +92,9 @@ class BaseConfig(BaseModel):
                 out += type(default).get_template_str(indent=indent, level=level + 1)
             elif isinstance(default, Enum):
                 out += json.dumps(default.value)
-            elif default is not None:
+            elif default is None or type(default).__name__ == "PydanticUndefinedType":
+                out += "null"  # required fields have no default: the template shows where to fill them in
+            else:
                 try:
                     out += json.dumps(_jsonable(default))
                 except TypeError:
@@ -101,6 +103,26 @@ class BaseConfig(BaseModel):
                 out += ","
             out += "\n"
         return out + " " * indent * (level - 1) + "}"
+
+    def as_annotated_str(self, indent: int = 4, level: int = 1) -> str:
+        """This instance's values rendered like the template: every field preceded by its description as a comment.
+        The result is YAML (JSON with ``#`` comments) that ``from_yaml`` reads back."""
+        pad = " " * indent * level
+        names = list(type(self).model_fields.keys())
+        out = "{\n" + f"{pad}# {type(self).__name__}\n"
+        for i, name in enumerate(names):
+            info = type(self).model_fields[name]
+            value = getattr(self, name)
+            for line in (info.description or "").split("\n"):
+                if line.strip():
+                    out += f"{pad}# {line}\n"
+            out += pad + f'"{name}": '
+            if isinstance(value, BaseConfig):
+                out += value.as_annotated_str(indent=indent, level=level + 1)
+            else:
+                out += json.dumps(_jsonable(value))
+            out += ("," if i != len(names) - 1 else "") + "\n\n"
+        return out.rstrip("\n") + "\n" + " " * indent * (level - 1) + "}"
 
     @classmethod
     def save_template(cls, out_file: Union[str, Path], indent: int = 4) -> None:

@@ -13,7 +13,7 @@ from .linear import ColumnParallelLinear, RowParallelLinear, VocabParallelEmbedd
 from .lora import LoRaConfig, LoRAModuleType, ParallelLoRa  # noqa: F401
 from .mlp import ParallelMLP, ParallelSwiGLUMLP  # noqa: F401
 from .norms import LayerNorm, LayerNormConfig, LayerNormOptimizationType, NormType, RMSNorm, get_norm  # noqa: F401
-from .p2p import GradOutput, PipeCommunicator  # noqa: F401
+from .p2p import CommunicationMetaBase, GradOutput, ModelParallelCommunicator, PipeCommunicator  # noqa: F401
 from .parameter_meta import CoreParameterMeta  # noqa: F401
 from .partition import (  # noqa: F401
     PipePartitionCoordinates,

@@ -138,3 +138,93 @@ class PipeCommunicator:
                 tensors.append(x)
                 grads.append(self._recv_into(tuple(x.shape), x.dtype, origin_global_rank))
         return GradOutput(tensors, grads)
+
+
+class ModelParallelCommunicator:
+    """Broadcast an arbitrary pytree from TP rank 0 to its tensor-parallel group (reference communicator.py:513-759;
+    unused by the training path, kept for inference-style input sync).
+
+    Same protocol as :class:`PipeCommunicator` with broadcasts instead of send/recv: the first call (and every call
+    under ``use_continuous_recommunication``, or after :meth:`reset_communication_meta`) ships the pickled structure
+    (treespec + per-leaf shape/dtype/requires_grad, non-tensor leaves by value), then one broadcast per tensor leaf.
+    """
+
+    def __init__(self, topology: Any, use_continuous_recommunication: bool = False):
+        self.topology = topology
+        self.local_device = topology.device
+        self._use_continuous_recommunication = use_continuous_recommunication
+        self.byte_wire = self.local_device.type != "cuda"
+        self._meta: Optional[CommunicationMetaBase] = None
+
+    @property
+    def _src(self) -> int:
+        return self.topology.model_parallel_ranks[0]
+
+    def _bcast(self, t: torch.Tensor) -> None:
+        dist.broadcast(t, src=self._src, group=self.topology.model_parallel_group)
+
+    def _bcast_object(self, obj: Any = None) -> Any:
+        sender = self.topology.model_parallel_rank == 0
+        if sender:
+            payload = torch.frombuffer(bytearray(pickle.dumps(obj)), dtype=torch.uint8).to(self.local_device)
+            n = torch.tensor([payload.numel()], dtype=torch.long, device=self.local_device)
+        else:
+            n = torch.zeros(1, dtype=torch.long, device=self.local_device)
+        self._bcast(n)
+        if not sender:
+            payload = torch.empty(int(n.item()), dtype=torch.uint8, device=self.local_device)
+        self._bcast(payload)
+        return obj if sender else pickle.loads(payload.cpu().numpy().tobytes())
+
+    def _needs_meta(self) -> bool:
+        return self._meta is None or self._use_continuous_recommunication
+
+    def send_data(self, data: Any) -> None:
+        leaves, spec = tree_flatten(data)
+        if self._needs_meta():
+            described = tuple(("t", tuple(x.shape), x.dtype, bool(x.requires_grad)) if torch.is_tensor(x) else ("o", x)
+                              for x in leaves)
+            self._meta = CommunicationMetaBase(spec, described)
+            self._bcast_object(self._meta)
+        for x in leaves:
+            if torch.is_tensor(x):
+                self._bcast(_wire(x.to(self.local_device), self.byte_wire))
+
+    def recv_data(self) -> Any:
+        if self._needs_meta():
+            self._meta = self._bcast_object()
+        assert self._meta is not None
+        leaves = []
+        for d in self._meta.leaves:
+            if d[0] != "t":
+                leaves.append(d[1])
+                continue
+            _, shape, dtype, requires_grad = d
+            wire_dtype = torch.uint8 if dtype == torch.bool else dtype
+            if self.byte_wire:
+                n = int(torch.Size(shape).numel()) * torch.empty((), dtype=wire_dtype).element_size()
+                buf = torch.empty(n, dtype=torch.uint8, device=self.local_device)
+                self._bcast(buf)
+                t = buf.view(wire_dtype).reshape(shape)
+            else:
+                t = torch.empty(shape, dtype=wire_dtype, device=self.local_device)
+                self._bcast(t)
+            t = t.to(torch.bool) if dtype == torch.bool else t
+            if requires_grad and t.is_floating_point():
+                t.requires_grad_(True)
+            leaves.append(t)
+        return tree_unflatten(leaves, self._meta.treespec)
+
+    def sync_data(self, data: Any) -> Any:
+        """TP rank 0 passes ``data`` and gets it back; every other rank passes anything (ignored) and receives it."""
+        if self.topology.config.model_parallel_size == 1:
+            return data
+        if self.topology.model_parallel_rank == 0:
+            self.send_data(data)
+            return data
+        return self.recv_data()
+
+    def reset_communication_meta(self, use_continuous_recommunication: Optional[bool] = None) -> None:
+        self._meta = None
+        if use_continuous_recommunication is not None:
+            self._use_continuous_recommunication = use_continuous_recommunication

@@ -61,3 +61,33 @@ def test_parameter_count_is_layout_invariant():
         out = dist_launcher(run_minimal, mp * pp, config_dict=base_config(mp, pp, 1, iters=1, tying=True), return_state=True)
         counts.add(out[0]["params_count"][1])
     assert len(counts) == 1, counts
+
+
+def _mp_comm_worker(rank: int, world_size: int, master_port: int):
+    import torch
+
+    from scaling_b200.core import Topology, TopologyConfig
+    from scaling_b200.core.nn import ModelParallelCommunicator
+
+    topo = Topology(TopologyConfig(model_parallel_size=2, pipe_parallel_size=1, data_parallel_size=1, global_rank=rank,
+                                   micro_batch_size=1, gradient_accumulation_steps=1))
+    topo.initialize_distributed("127.0.0.1", str(master_port))
+    comm = ModelParallelCommunicator(topo)
+    tree = {"a": torch.arange(6.0).reshape(2, 3), "b": [torch.tensor([True, False]), 7, "x"], "c": None}
+    got = comm.sync_data(tree if rank == 0 else None)
+    assert got["b"][1:] == [7, "x"] and got["c"] is None
+    assert torch.equal(got["a"].cpu(), torch.arange(6.0).reshape(2, 3)) and got["b"][0].tolist() == [True, False]
+    # same structure: only payloads travel
+    got = comm.sync_data({"a": tree["a"] + 1, "b": tree["b"], "c": None} if rank == 0 else None)
+    assert torch.equal(got["a"].cpu(), torch.arange(6.0).reshape(2, 3) + 1)
+    # a new structure needs a reset (or continuous recommunication)
+    comm.reset_communication_meta(use_continuous_recommunication=True)
+    got = comm.sync_data([torch.ones(4, dtype=torch.long)] if rank == 0 else None)
+    assert got[0].tolist() == [1, 1, 1, 1]
+    got = comm.sync_data((torch.zeros(2), 3) if rank == 0 else None)
+    assert got[1] == 3 and got[0].shape == (2,)
+    return True
+
+
+def test_model_parallel_communicator():
+    assert all(dist_launcher(_mp_comm_worker, 2).values())
