@@ -28,7 +28,28 @@ def init(**kwargs: Any) -> Iterator[Optional[Any]]:
         yield ctx
 
 
-def maybe_periodic_stacktraces(enabled: bool, interval_seconds: int = 30) -> None:
-    """Dump all thread stacks periodically (debugging hangs)."""
+@contextlib.contextmanager
+def maybe_periodic_stacktraces(enabled: bool, interval_seconds: int = 30) -> Iterator[None]:
+    """While the block runs, dump all thread stacks every ``interval_seconds`` (debugging hangs)."""
     if enabled:
         faulthandler.dump_traceback_later(interval_seconds, repeat=True)
+    try:
+        yield
+    finally:
+        if enabled:
+            faulthandler.cancel_dump_traceback_later()
+
+
+@contextlib.contextmanager
+def determined_profiler_from_ctx(core_context: Any, experiment_config: Any, info: Any) -> Iterator[Optional[Any]]:
+    """Determined's system-metrics profiler agent for this trial, or ``None`` when Determined (or its profiler API,
+    which newer releases dropped) is not available."""
+    try:
+        from determined.profiler import ProfilerAgent  # type: ignore
+    except Exception:  # noqa: BLE001
+        yield None
+        return
+    agent = ProfilerAgent.from_env(info, core_context.distributed.rank if core_context is not None else 0,
+                                   core_context.distributed.local_rank if core_context is not None else 0)
+    with agent:
+        yield agent
