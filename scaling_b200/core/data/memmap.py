@@ -73,7 +73,8 @@ class MemoryMapDataset(_PrefixFiles):
     def __getitem__(self, idx: int) -> np.ndarray:
         if not isinstance(idx, (int, np.integer)):
             raise NotImplementedError
-        assert idx < self.document_count, f"cannot retrieve document idx {idx} from {self.document_count} documents"
+        if not 0 <= idx < self.document_count:
+            raise IndexError(f"cannot retrieve document idx {idx} from {self.document_count} documents")
         start, size = (int(x) for x in self._index[idx])
         return self._data[start:start + size]
 
@@ -232,7 +233,8 @@ class FileDataset(_PrefixFiles):
         return full[:, 1]
 
     def __getitem__(self, idx: int) -> np.ndarray:
-        assert idx < self.document_count, f"cannot retrieve document idx {idx} from {self.document_count} documents"
+        if not 0 <= idx < self.document_count:
+            raise IndexError(f"cannot retrieve document idx {idx} from {self.document_count} documents")
         start, size = self._index_row(idx)
         return self._read(self._data_handle, self.dtype, size, start)
 

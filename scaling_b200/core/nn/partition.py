@@ -26,6 +26,8 @@ def pipe_partition_from_indices(partition_array: Sequence[int], num_layers: Opti
     if num_layers is not None and partition_array[-1] != num_layers:
         raise ValueError(f"Last entry of partition_array needs to match num_layers; got partition_array="
                          f"{list(partition_array)}, num_layers={num_layers}.")
+    if len(partition_array) < 2 or partition_array[0] != 0 or any(e <= s for s, e in zip(partition_array[:-1], partition_array[1:])):
+        raise ValueError(f"partition_array must start at 0 and be strictly increasing (no empty stage); got {list(partition_array)}")
     return [PipePartitionCoordinates(int(s), int(e)) for s, e in zip(partition_array[:-1], partition_array[1:])]
 
 
