@@ -77,7 +77,7 @@ def run_bench(args: Any, bench: Any) -> None:
     # ---- phase 1: device-timed, inputs staged on the GPU -----------------------------------------------------
     real_loader = trainer.dataloader
     if real_loader is not None:
-        trainer.dataloader = _StagedLoader(real_loader, gas * 2, topo.device)
+        trainer.dataloader = _StagedLoader(real_loader, gas * (args.warmup + args.steps), topo.device)  # no batch repeats
     _lib.reset_launch_count()
     launches_before = [0]
 
