@@ -57,6 +57,11 @@ struct Params {
   int ldaux;
   int swiglu_up_row_offset;
   int tiles_m, tiles_n;
+  // split-K tail: the last, partial wave of tiles is cut along K into `split` parts so that it fills the machine
+  int full_tiles;   // tiles [0, full_tiles) run whole; the remaining `num_tiles - full_tiles` are split
+  int split;        // parts per tail tile (1 = no splitting)
+  float* split_ws;  // [tail tile][part][cta half] partial accumulators, 128x256 fp32 each
+  unsigned int* split_counters;  // [tail tile][cta half] arrivals; the last arriver reduces and resets
   // kAllReduce only
   int tp_rank, tp_size;
   uint32_t epoch;
@@ -73,6 +78,7 @@ struct __align__(8) Barriers {
   uint64_t acc_full[kAccStages];
   uint64_t acc_empty[kAccStages];
   uint32_t tmem_base;
+  uint32_t split_last;  // split-K: 1 when this CTA is the last part of its tile to arrive
   uint32_t pushed;  // kAllReduce: epilogue-warp tile pushes completed (4 per CTA tile), read by the signal warp
 };
 
@@ -199,6 +205,62 @@ SB_DEVICE void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
   tn = r / gsize;
 }
 
+// Work unit u of the persistent schedule -> (tile, k-block range, part index or -1 when the tile is not split).
+struct Unit {
+  int tile, kb0, kb1, part;
+};
+SB_DEVICE Unit get_unit(int u, const Params& p, int k_blocks) {
+  Unit w;
+  if (u < p.full_tiles) {
+    w.tile = u, w.kb0 = 0, w.kb1 = k_blocks, w.part = -1;
+  } else {
+    const int r = u - p.full_tiles;
+    w.tile = p.full_tiles + r / p.split;
+    w.part = r % p.split;
+    w.kb0 = (int)((long long)w.part * k_blocks / p.split);
+    w.kb1 = (int)((long long)(w.part + 1) * k_blocks / p.split);
+  }
+  return w;
+}
+constexpr int kCtaAccFloats = 128 * 256;
+// Partial accumulators are stored "float4-column-major": [group of 4 columns][row][4] so that a warp (lane = row) writes
+// and later reads 512 contiguous bytes per instruction.
+SB_DEVICE float4* split_slot(const Params& p, int tail_tile, int part, uint32_t half) {
+  return reinterpret_cast<float4*>(p.split_ws + ((size_t)(tail_tile * p.split + part) * 2 + half) * kCtaAccFloats);
+}
+// v[0..n) += the other parts' partials of columns [c, c+n) of this thread's row, in part order (own registers take the
+// place of part `own`), so the sum is the same whichever part arrives last.
+template <int kN>
+SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, int tail_tile, int own, uint32_t half, int row_in_cta, int c) {
+  float acc[kN];
+  bool first = true;
+  for (int q = 0; q < p.split; ++q) {
+    if (q == own) {
+      if (first) {
+#pragma unroll
+        for (int i = 0; i < kN; ++i) acc[i] = __uint_as_float(v[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < kN; ++i) acc[i] += __uint_as_float(v[i]);
+      }
+    } else {
+      const float4* src = split_slot(p, tail_tile, q, half) + (size_t)(c >> 2) * 128 + row_in_cta;
+#pragma unroll
+      for (int g = 0; g < kN / 4; ++g) {
+        const float4 x = __ldcg(src + (size_t)g * 128);
+        if (first) {
+          acc[4 * g] = x.x, acc[4 * g + 1] = x.y, acc[4 * g + 2] = x.z, acc[4 * g + 3] = x.w;
+        } else {
+          acc[4 * g] += x.x, acc[4 * g + 1] += x.y, acc[4 * g + 2] += x.z, acc[4 * g + 3] += x.w;
+        }
+      }
+    }
+    first = false;
+  }
+#pragma unroll
+  for (int i = 0; i < kN; ++i) v[i] = __float_as_uint(acc[i]);
+}
+
 template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kEpi == kAllReduce ? kArThreads : kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
@@ -212,6 +274,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const bool leader = rank == 0;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int k_blocks = (p.K + BK - 1) / BK;
+  const int num_units = p.full_tiles + (num_tiles - p.full_tiles) * p.split;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
 
@@ -242,12 +305,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      for (int u = cluster_id; u < num_units; u += num_clusters) {
+        const Unit w = get_unit(u, p, k_blocks);
         int tm, tn;
-        tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+        tile_coords(w.tile, p.tiles_m, p.tiles_n, tm, tn);
         const int m0 = tm * BM + rank * 128;
         const int nb = (kEpi == kSwiGLU) ? tn * (BN / 2) + (rank ? p.swiglu_up_row_offset : 0) : tn * BN + rank * 128;
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = w.kb0; kb < w.kb1; ++kb) {
           mbar_wait(&bars->empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * kStageBytes;
           uint8_t* sb_ = sa + kABytes;
@@ -280,11 +344,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      for (int u = cluster_id; u < num_units; u += num_clusters) {
+        const Unit w = get_unit(u, p, k_blocks);
         mbar_wait(&bars->acc_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = w.kb0; kb < w.kb1; ++kb) {
           mbar_wait(&bars->full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * kStageBytes);
@@ -295,7 +360,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
                                           : make_smem_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = kBMajorMN ? make_smem_desc_sw128(sb_ + k * 2048, 8192, 1024)
                                           : make_smem_desc_sw128(sb_ + k * 32, 16, 1024);
-            umma_f16_ss_2sm(tmem_d, da, db, idesc, (kb | k) != 0);
+            umma_f16_ss_2sm(tmem_d, da, db, idesc, ((kb - w.kb0) | k) != 0);
           }
           umma_commit_2sm(&bars->empty[stage]);
           if (++stage == kStages) {
@@ -446,14 +511,56 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     const int ew = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+    for (int u = cluster_id; u < num_units; u += num_clusters) {
+      const Unit w = get_unit(u, p, k_blocks);
       int tm, tn;
-      tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-      const int row = tm * BM + rank * 128 + ew * 32 + lane;
+      tile_coords(w.tile, p.tiles_m, p.tiles_n, tm, tn);
+      const int row_in_cta = ew * 32 + lane;
+      const int row = tm * BM + rank * 128 + row_in_cta;
       mbar_wait(&bars->acc_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
       const bool row_ok = row < p.M;
+      const bool split = w.part >= 0;
+      const int tail_tile = w.tile - p.full_tiles;
+      if (split) {
+        // park this part's accumulator, then find out whether the other parts are already in
+        float4* mine = split_slot(p, tail_tile, w.part, rank) + row_in_cta;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            __stcg(mine + (size_t)((c >> 2) + g) * 128,
+                   make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                               __uint_as_float(v[4 * g + 3])));
+        }
+        __threadfence();
+        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        if (ew == 0 && lane == 0) {
+          unsigned int* ctr = p.split_counters + tail_tile * 2 + rank;
+          const unsigned int old = atomicAdd(ctr, 1u);
+          const bool last = old == (unsigned int)(p.split - 1);
+          if (last) *ctr = 0;  // every part has arrived: leave the counter clean for the next launch
+          bars->split_last = last ? 1u : 0u;
+        }
+        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        const bool last = bars->split_last != 0;
+        asm volatile("bar.sync 1, 128;\n" ::: "memory");  // flag consumed before the next tile may overwrite it
+        if (!last) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
+          if (++acc == kAccStages) {
+            acc = 0;
+            acc_phase ^= 1;
+          }
+          continue;
+        }
+        __threadfence();
+      }
 
       if (kEpi == kSwiGLU) {
         const int n0 = tn * (BN / 2);
@@ -465,6 +572,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           tmem_ld_32x32b_x16(taddr + c, g);
           tmem_ld_32x32b_x16(taddr + BN / 2 + c, u);
           tmem_ld_wait();
+          if (split) {
+            split_reduce_chunk<16>(g, p, tail_tile, w.part, rank, row_in_cta, c);
+            split_reduce_chunk<16>(u, p, tail_tile, w.part, rank, row_in_cta, BN / 2 + c);
+          }
           if (row_ok && n0 + c < p.N) {
             uint32_t o[8], pg[8], pu[8];
 #pragma unroll
@@ -508,6 +619,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           uint32_t v[32];
           tmem_ld_32x32b_x32(taddr + c, v);
           tmem_ld_wait();
+          if (split) split_reduce_chunk<32>(v, p, tail_tile, w.part, rank, row_in_cta, c);
           const int col = n0 + c;
           if (!row_ok || col >= p.N) continue;
           if (col + 32 <= p.N) {
@@ -612,8 +724,39 @@ static int num_sms() {
   return n;
 }
 
+// Persistent workspace of the split-K tail (one per device; the library serialises its use on the launching stream —
+// GEMMs of this library issued concurrently on several streams of one device must disable splitting).
+struct SplitWorkspace {
+  float* ws = nullptr;
+  unsigned int* counters = nullptr;
+};
+static SplitWorkspace* split_workspace() {
+  static SplitWorkspace table[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  SplitWorkspace& w = table[dev & 63];
+  if (!w.ws) {
+    const size_t partial_bytes = (size_t)num_sms() * kCtaAccFloats * sizeof(float);
+    const size_t counter_bytes = (size_t)num_sms() * sizeof(unsigned int);
+    void* base = nullptr;
+    if (cudaMalloc(&base, partial_bytes + counter_bytes) != cudaSuccess) return nullptr;
+    cudaMemset(static_cast<char*>(base) + partial_bytes, 0, counter_bytes);
+    w.ws = static_cast<float*>(base);
+    w.counters = reinterpret_cast<unsigned int*>(static_cast<char*>(base) + partial_bytes);
+  }
+  return &w;
+}
+static bool split_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("SCALING_B200_GEMM_SPLITK");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
 template <int AM, int BMj, int EPI, typename OutT>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream, int max_ctas) {
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaStream_t stream, int max_ctas) {
   auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
   static bool configured = false;
   if (!configured) {
@@ -621,10 +764,31 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
                                        (int)(EPI == kAllReduce ? kArSmemBytes : kSmemBytes)));
     configured = true;
   }
-  int tiles = p.tiles_m * p.tiles_n;
-  int clusters = num_sms() / 2;
-  if (tiles < clusters) clusters = tiles;
-  if (max_ctas > 0 && clusters > max_ctas / 2) clusters = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
+  const int tiles = p.tiles_m * p.tiles_n;
+  int width = num_sms() / 2;  // clusters the machine runs at once
+  if (max_ctas > 0 && width > max_ctas / 2) width = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
+  p.full_tiles = tiles, p.split = 1;
+  // Wave quantisation: 256 tiles on 74 clusters are 3.46 waves, i.e. the machine idles 13 % of the kernel.  Cut the
+  // tiles of the last, partial wave along K so that they occupy (almost) every cluster; the parts meet in an fp32
+  // workspace and the last one to arrive runs the epilogue on the sum.
+  if (EPI != kAllReduce && split_enabled()) {
+    const int rem = tiles % width;
+    const int k_blocks = (p.K + BK - 1) / BK;
+    int parts = rem > 0 ? width / rem : 1;
+    // Measured on B200 (profiles/kbench_r1_splitk.json): parking and re-reading the 128 KiB partials costs 10-25 us per
+    // tail, and the un-split tail already runs at boosted clocks (half the SMs idle under the power cap), so splitting
+    // pays only when each part still holds >= 112 k-blocks (K >= 14336 for two parts).
+    if (parts > 4) parts = 4;
+    if (parts > k_blocks / 112) parts = k_blocks / 112;
+    if (parts >= 2) {
+      if (SplitWorkspace* w = split_workspace()) {
+        p.split = parts, p.full_tiles = tiles - rem;
+        p.split_ws = w->ws, p.split_counters = w->counters;
+      }
+    }
+  }
+  const int units = p.full_tiles + (tiles - p.full_tiles) * p.split;
+  const int clusters = units < width ? units : width;
   if (EPI == kAllReduce)
     kern<<<clusters * 2, kArThreads, kArSmemBytes, stream>>>(ta, tb, p);
   else

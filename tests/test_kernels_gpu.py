@@ -43,6 +43,38 @@ def test_gemm_layouts(K, M, N, K_, a_mn, b_mn):
     assert _rel_err(out32, ref) < 1e-4, _rel_err(out32, ref)
 
 
+@pytest.mark.parametrize("M,N,K_", [(512, 512, 14336), (4096, 4096, 14336), (1000, 520, 28680), (2048, 1024, 32768)])
+def test_gemm_split_k_tail(K, M, N, K_):
+    """Shapes whose last wave of 256x256 tiles is partial: the tail tiles are split along K and reduced through the
+    fp32 workspace (2-CTA kernel).  Every epilogue must see the full sum, and repeated launches must agree bitwise
+    (the part order of the reduction is fixed, the arrival counters reset themselves)."""
+    torch.manual_seed(5)
+    a = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(N, K_, device="cuda", dtype=torch.bfloat16) / math.sqrt(K_)
+    ref = a.float() @ b.float().t()
+    out = K.gemm(a, b, out_dtype=torch.float32)
+    assert _rel_err(out, ref) < 1e-4, _rel_err(out, ref)
+    for _ in range(3):
+        assert torch.equal(K.gemm(a, b, out_dtype=torch.float32), out)
+    assert _rel_err(K.gemm(a, b), ref) < 1e-2
+    bt = b.t().contiguous()
+    assert _rel_err(K.gemm(a, bt, b_mn=True, out_dtype=torch.float32), ref) < 1e-4
+    at = a.t().contiguous()
+    assert _rel_err(K.gemm(at, bt, a_mn=True, b_mn=True, out_dtype=torch.float32), ref) < 1e-4
+    acc = torch.randn(M, N, device="cuda", dtype=torch.float32)
+    want = acc + ref
+    K.gemm(a, b, out=acc, accumulate=True)
+    assert _rel_err(acc, want) < 1e-4
+    bias = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    assert _rel_err(K.gemm(a, b, bias=bias), ref + bias.float()) < 1e-2
+    if N % 16 == 0:
+        F = N // 2
+        h, pre = K.gemm_swiglu(a, b)
+        g, u = ref[:, :F].bfloat16().float(), ref[:, F:].bfloat16().float()
+        assert _rel_err(pre[:, :F], g) < 1e-2 and _rel_err(pre[:, F:], u) < 1e-2
+        assert _rel_err(h, torch.nn.functional.silu(g) * u) < 2e-2
+
+
 def test_gemm_accumulate_and_bias(K):
     torch.manual_seed(1)
     M, N, K_ = 512, 768, 320

@@ -25,11 +25,15 @@ from scaling_b200.transformer.train import build_trainer  # noqa: E402
 OF.set_ops(a.ops)
 OF.set_plain_gemm(a.plain_gemm)
 ATT.set_attention_impl(a.attention)
-args = argparse.Namespace(gpus=1, steps=1, warmup=1, layers=a.layers, ops=a.ops, act_ckpt="disabled", seqs_per_gpu=4)
+import os  # noqa: E402
+
+rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+args = argparse.Namespace(gpus=world, steps=1, warmup=1, layers=a.layers, ops=a.ops, act_ckpt="disabled", seqs_per_gpu=4, layout=None)
 prefix = Path("/tmp/scaling_prof") / "data"
-bench.write_synthetic_dataset(prefix, n_docs=64, vocab=32000, rank=0)
-cfg = bench.model_config(args, 1, prefix)
-trainer = build_trainer(LaunchConfig(master_port=29533, master_addr="127.0.0.1", world_size=1, global_rank=0, local_slot=0, payload=cfg))
+bench.write_synthetic_dataset(prefix, n_docs=64 * world, vocab=32000, rank=rank)
+cfg = bench.model_config(args, world, prefix)
+trainer = build_trainer(LaunchConfig(master_port=int(os.environ.get("MASTER_PORT", 29533)), master_addr="127.0.0.1",
+                                     world_size=world, global_rank=rank, local_slot=rank, payload=cfg))
 for _ in range(2):
     trainer.train_step()
 torch.cuda.synchronize()
@@ -39,7 +43,11 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     out = trainer.train_step()
     torch.cuda.synchronize()
 table = prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=90)
-Path("gpurun_out").mkdir(exist_ok=True)
-Path(f"gpurun_out/profile_step_{a.tag}.txt").write_text(table + f"\nstep_duration {out.step_duration}\n")
-print(table[-6000:])
-print("step_duration", out.step_duration)
+if rank == 0:
+    Path("gpurun_out").mkdir(exist_ok=True)
+    Path(f"gpurun_out/profile_step_{a.tag}.txt").write_text(table + f"\nstep_duration {out.step_duration}\n")
+    print(table[-6000:])
+    print("step_duration", out.step_duration)
+if torch.distributed.is_initialized():
+    torch.distributed.barrier()
+    torch.distributed.destroy_process_group()
