@@ -45,6 +45,53 @@ def _kernel_worker(rank: int, world_size: int, master_port: int):
     return worst
 
 
+def _stress_worker(rank: int, world_size: int, master_port: int, iters: int):
+    """Signal/wait protocol under skew: ranks are delayed by random amounts before (and between) launches, shapes and
+    layouts change from call to call, and results are checked against NCCL every time.  A lost flag, a stale-parity
+    read or a premature buffer reuse shows up as a mismatch or as the kernel's 30 s watchdog trap."""
+    import random
+
+    import torch.distributed as dist
+
+    from scaling_b200.ops import kernels as K
+    from scaling_b200.parallel.symm import TPComm
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{master_port}", rank=rank, world_size=world_size,
+                            device_id=torch.device("cuda", rank))
+    comm = TPComm(dist.group.WORLD, torch.device("cuda", rank))
+    shapes = [(256, 128, 64, False), (1024, 512, 256, True), (4096, 4096, 128, False), (768, 1280, 192, True),
+              (2048, 256, 1024, False)]
+    gen = torch.Generator(device="cuda").manual_seed(100 + rank)
+    data = {}
+    for (M, N, Kd, b_mn) in shapes:
+        a = torch.randn(M, Kd, device="cuda", generator=gen).bfloat16()
+        b = (torch.randn((Kd, N) if b_mn else (N, Kd), device="cuda", generator=gen) * 0.1).bfloat16()
+        want = K.gemm(a, b, b_mn=b_mn, out_dtype=torch.float32)
+        dist.all_reduce(want)
+        data[(M, N, Kd, b_mn)] = (a, b, want)
+    order = random.Random(7)       # same call sequence on every rank
+    jitter = random.Random(rank)   # different delays on every rank
+    worst = 0.0
+    for i in range(iters):
+        shape = order.choice(shapes)
+        a, b, want = data[shape]
+        if jitter.random() < 0.5:
+            torch.cuda._sleep(int(jitter.random() * 3_000_000))  # up to ~2 ms of device-side skew
+        out = K.gemm_allreduce(a, b, comm, b_mn=shape[3])
+        if i % 8 == 0 or i > iters - 4:
+            err = ((out.float() - want).abs().max() / want.abs().max()).item()
+            assert err < 2e-2, (i, shape, err)
+            worst = max(worst, err)
+    torch.cuda.synchronize()
+    return worst
+
+
+def test_gemm_allreduce_protocol_stress():
+    res = dist_launcher(_stress_worker, world_size=2, timeout=400, iters=300)
+    assert all(v < 2e-2 for v in res.values())
+
+
 def test_gemm_allreduce_kernel():
     res = dist_launcher(_kernel_worker, world_size=2, timeout=300)
     assert all(v < 2e-2 for v in res.values())

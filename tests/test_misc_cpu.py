@@ -1,0 +1,303 @@
+"""Pipe communication of arbitrary pytrees, runner/launcher on localhost, text dataset packing, blended dataset,
+loss scaler, FLOP helpers, inference-vs-training consistency (reference: tests/core/test_nn/test_pipe_communication.py,
+test_runner/test_runner.py, tests/transformer/test_data.py, test_blended_dataset.py, test_utils.py,
+tests/core/test_nn/test_inference_module.py)."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from tests.utils import dist_launcher, find_free_port
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+# ------------------------------------------------------------------------------------------ pipe communication
+class _Custom:
+    def __init__(self, v):
+        self.v = v
+
+    def __eq__(self, o):
+        return isinstance(o, _Custom) and o.v == self.v
+
+
+def _trees():
+    t = torch.arange(6.0).reshape(2, 3)
+    return [
+        t,
+        (t, t + 1),
+        [t, "a string", 3, None],
+        {"x": t, "y": {"z": (t * 2, 5.5)}},
+        (torch.tensor([True, False]), torch.arange(4), torch.ones(2, dtype=torch.bfloat16)),
+        {"arr": np.arange(3), "obj": _Custom(7), "t": t.requires_grad_(False)},
+        (torch.zeros(()), torch.ones(1, 1, 1)),
+        [],
+        ({"a": []}, (t,)),
+    ]
+
+
+def _equal(a, b):
+    if torch.is_tensor(a):
+        return torch.is_tensor(b) and a.dtype == b.dtype and a.shape == b.shape and torch.equal(a.cpu(), b.cpu())
+    if isinstance(a, np.ndarray):
+        return isinstance(b, np.ndarray) and (a == b).all()
+    if isinstance(a, dict):
+        return isinstance(b, dict) and a.keys() == b.keys() and all(_equal(a[k], b[k]) for k in a)
+    if isinstance(a, (list, tuple)):
+        return type(a) is type(b) and len(a) == len(b) and all(_equal(x, y) for x, y in zip(a, b))
+    return a == b
+
+
+def _pipe_worker(rank: int, world_size: int, master_port: int, continuous: bool):
+    import torch.distributed as dist
+
+    from scaling_b200.core.nn import PipeCommunicator
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{master_port}", rank=rank, world_size=world_size)
+    dev = torch.device("cpu")
+    ok = []
+    for tree in _trees():
+        comm = PipeCommunicator(dev, recv_grads=rank == 0, recv_data=rank == 1, use_continuous_recommunication=continuous)
+        for rep in range(2):  # second round: metadata is cached (or re-sent under continuous recommunication)
+            if rank == 0:
+                comm.send_data(tree, target_global_rank=1)
+                comm.drain()
+            else:
+                ok.append(_equal(comm.recv_data(origin_global_rank=0), tree))
+    # activation + gradient round trip: only differentiable leaves get gradients back
+    comm = PipeCommunicator(dev, recv_grads=rank == 0, recv_data=rank == 1)
+    x = torch.randn(3, 4, requires_grad=True)
+    payload = (x * 2, torch.arange(3), "meta")
+    if rank == 0:
+        comm.send_data(payload, target_global_rank=1)
+        g = comm.recv_gradients(payload, origin_global_rank=1)
+        assert len(g.tensors) == 1 and g.tensors[0] is payload[0]
+        torch.autograd.backward(g.tensors, g.grad_tensors)
+        ok.append(torch.allclose(x.grad, torch.full_like(x, 6.0)))
+    else:
+        got = comm.recv_data(origin_global_rank=0)
+        assert got[0].requires_grad and not got[1].requires_grad and got[2] == "meta"
+        (got[0] * 3).sum().backward()
+        comm.send_gradients(got, target_global_rank=0)
+        comm.drain()
+    return all(ok)
+
+
+@pytest.mark.parametrize("continuous", [False, True])
+def test_pipe_communicator_pytrees(continuous):
+    assert all(dist_launcher(_pipe_worker, 2, continuous=continuous).values())
+
+
+# ------------------------------------------------------------------------------------------------------ runner
+@pytest.mark.parametrize("hosts,expect", [(["localhost slots=2"], 2), (["localhost slots=0,1,2"], 3), (["localhost"], 2)])
+def test_runner_starts_one_process_per_slot(tmp_path, hosts, expect):
+    """runner_main on localhost: N processes, each with the launcher env contract and the decoded payload."""
+    script = tmp_path / "proc.py"
+    script.write_text(
+        "import json, os, sys\n"
+        f"sys.path.insert(0, {str(ROOT)!r})\n"
+        "from scaling_b200.core import LaunchConfig\n"
+        "lc = LaunchConfig.from_launcher_args()\n"
+        "out = dict(rank=lc.global_rank, world=lc.world_size, slot=lc.local_slot, addr=lc.master_addr, port=lc.master_port, payload=lc.payload)\n"
+        f"json.dump(out, open(os.path.join({str(tmp_path)!r}, f'process_{{lc.global_rank}}.json'), 'w'))\n")
+    driver = tmp_path / "drive.py"
+    port = find_free_port()
+    driver.write_text(
+        "import sys\n"
+        f"sys.path.insert(0, {str(ROOT)!r})\n"
+        "from scaling_b200.core import RunnerConfig, runner_main\n"
+        f"cfg = RunnerConfig(hosts={hosts!r}, script={str(script)!r}, master_port={port}, master_addr='127.0.0.1', default_gpu_count=2)\n"
+        "runner_main(cfg, payload={'hello': [1, 2, {'x': 'y'}]})\n")
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    subprocess.run([sys.executable, str(driver)], check=True, cwd=str(ROOT), env=env, timeout=120)
+    files = sorted(tmp_path.glob("process_*.json"))
+    assert len(files) == expect
+    recs = [json.load(open(f)) for f in files]
+    assert sorted(r["rank"] for r in recs) == list(range(expect))
+    assert all(r["world"] == expect and r["port"] == port and r["payload"] == {"hello": [1, 2, {"x": "y"}]} for r in recs)
+
+
+def test_launcher_propagates_failure(tmp_path):
+    script = tmp_path / "fail.py"
+    script.write_text("import os, sys, time\nif os.environ['RANK'] == '1':\n    sys.exit(3)\ntime.sleep(60)\n")
+    driver = tmp_path / "drive.py"
+    driver.write_text(
+        "import sys\n"
+        f"sys.path.insert(0, {str(ROOT)!r})\n"
+        "from scaling_b200.core import RunnerConfig, runner_main\n"
+        f"runner_main(RunnerConfig(hosts=['localhost slots=2'], script={str(script)!r}, master_port={find_free_port()}, master_addr='127.0.0.1'), payload={{}})\n")
+    r = subprocess.run([sys.executable, str(driver)], cwd=str(ROOT), env=dict(os.environ, PYTHONPATH=str(ROOT)), timeout=60)
+    assert r.returncode != 0  # the sibling that sleeps is killed; the job does not hang for 60 s
+
+
+# ------------------------------------------------------------------------------------------------------- data
+def _corpus(prefix: Path, sizes, seed=0):
+    from scaling_b200.core import MemoryMapDatasetBuilder
+
+    rng = np.random.default_rng(seed)
+    prefix.parent.mkdir(parents=True, exist_ok=True)
+    with MemoryMapDatasetBuilder(prefix) as b:
+        for n in sizes:
+            d = rng.integers(1, 100, size=n)
+            d[-1] = 0
+            b.add(d)
+
+
+def test_text_dataset_packs_without_padding(tmp_path):
+    from scaling_b200.transformer.data import TextDataset, TextDatasetBatch
+
+    sizes = [5, 40, 3, 17, 64, 9, 30]
+    _corpus(tmp_path / "c", sizes)
+    ds = TextDataset(tmp_path / "c", sequence_length=16, seed=1, shuffle=False)
+    total = sum(sizes)
+    stream = np.concatenate([np.asarray(ds.memory_map[i]) for i in range(len(sizes))])
+    # every item is a contiguous 17-token slice of the document stream (no padding, documents straddle windows);
+    # consecutive windows overlap by the one token that is the last target of one and the first input of the next —
+    # except when a window ends exactly on an end-of-document token, then the next one starts with the next document
+    start = 0
+    for i in range(len(ds)):
+        w = ds[i].token_ids.tolist()
+        assert len(w) == 17 and w == stream[start:start + 17].tolist(), i
+        start += 17 if stream[start + 16] == 0 and start + 17 < len(stream) and False else 16
+        if w[-1] == 0:  # window closed on an EOD token: no overlap into the next document
+            start += 1
+    assert total - start < 17 + 1  # the tail that does not fill a window is dropped
+    batch = ds.collate([ds[0], ds[1]])
+    synced = TextDataset.sync_batch_to_model_parallel(None, batch)
+    assert isinstance(synced, TextDatasetBatch)
+    assert torch.equal(synced.input_token_ids[:, 1:], synced.target_token_ids[:, :-1])
+    # positions restart after every end-of-document token and cu_seqlens mark the document boundaries
+    ids, pos = synced.input_token_ids, synced.position_ids
+    for r in range(2):
+        for t in range(1, 16):
+            assert pos[r, t] == (0 if ids[r, t - 1] == 0 else pos[r, t - 1] + 1)
+    cu = synced.cumulative_seq_lengths.tolist()
+    assert cu[0] == 0 and cu[-1] == 32 and cu == sorted(set(cu))
+    # shuffling permutes documents deterministically; the index is cached next to the data
+    a = TextDataset(tmp_path / "c", 16, seed=3)
+    b = TextDataset(tmp_path / "c", 16, seed=3)
+    assert [a[i].token_ids.tolist() for i in range(len(a))] == [b[i].token_ids.tolist() for i in range(len(b))]
+    assert any(p.name.startswith("c_window_index_seed_3") for p in tmp_path.iterdir())
+    full = TextDataset(tmp_path / "c", 16, seed=1, shuffle=False, only_full_sequences=True)
+    docs = [np.asarray(full.memory_map[i]).tolist() for i in range(len(sizes))]
+    assert len(full) == sum((n - 1) // 16 for n in sizes)
+    for i in range(len(full)):  # only_full_sequences: a window never crosses a document boundary
+        w = full[i].token_ids.tolist()
+        assert any(w == d[k:k + 17] for d in docs for k in range(0, max(1, len(d) - 16), 16)), i
+
+
+def test_text_blended_dataset(tmp_path):
+    from scaling_b200.core import BlendedDatasetConfig
+    from scaling_b200.transformer.data import TextBlendedDataset, TextDataset
+
+    _corpus(tmp_path / "a", [50] * 20, seed=1)
+    _corpus(tmp_path / "b", [50] * 5, seed=2)
+    dsets = [TextDataset(tmp_path / n, 16, seed=0) for n in ("a", "b")]
+    cfg = BlendedDatasetConfig(cache_directory=tmp_path / "cache", weighted_sampler_alpha=1.0)
+    blend = TextBlendedDataset(seed=0, config=cfg, datasets=dsets)
+    assert len(blend) == len(dsets[0]) + len(dsets[1])  # alpha = 1: every item exactly once
+    idx = np.asarray(blend.dataset_indices)
+    assert np.bincount(idx[:, 0]).tolist() == [len(d) for d in dsets]
+    again = TextBlendedDataset(seed=0, config=cfg, datasets=dsets)
+    assert np.array_equal(np.asarray(again.dataset_indices), idx)
+    up = TextBlendedDataset(seed=0, config=BlendedDatasetConfig(cache_directory=tmp_path / "cache2", weighted_sampler_alpha=0.0),
+                            datasets=dsets)
+    counts = np.bincount(np.asarray(up.dataset_indices)[:, 0])
+    assert counts[0] == len(dsets[0]) // (len(dsets[0]) // len(dsets[1])) or counts[0] <= len(dsets[0])
+    assert blend[0].token_ids.shape == (17,)
+    shuffled = TextBlendedDataset(seed=0, config=BlendedDatasetConfig(cache_directory=tmp_path / "cache3", shuffle_dataset_indices=True),
+                                  datasets=dsets)
+    assert sorted(shuffled.random_index.tolist()) == list(range(len(shuffled)))
+
+
+# --------------------------------------------------------------------------------------------- optimizer bits
+def test_loss_scaler_dynamics():
+    from scaling_b200.core import LossScaler, LossScalerConfig
+
+    s = LossScaler(LossScalerConfig(enable=True, initial_scale=1024.0, window=3, hysteresis=2, min_scale=4.0))
+    assert s.scale == 1024.0
+    assert s.step(True).current_loss_scale == 1024.0  # first overflow only burns hysteresis
+    assert s.step(True).current_loss_scale == 512.0
+    out = [s.step(False).current_loss_scale for _ in range(5)]
+    assert out[-1] == 1024.0 and s.state_dict()["no_overflow_steps"] == 5
+    t = LossScaler(LossScalerConfig(enable=True))
+    t.load_state_dict(s.state_dict())
+    assert t.scale == s.scale
+    for _ in range(40):
+        s.step(True)
+    assert s.scale == 4.0  # clamped
+    off = LossScaler(LossScalerConfig(enable=False))
+    assert off.scale == 1.0 and off.step(None).overflow is None
+
+
+def test_flop_helpers():
+    from scaling_b200.core import Topology, TopologyConfig
+    from scaling_b200.transformer.config import TransformerArchitectureConfig
+    from scaling_b200.transformer.utils import (
+        HardwareType,
+        get_model_flop_utilization_palm,
+        get_tflops_aleph_alpha,
+        get_tflops_bloom,
+        get_tflops_electra,
+        get_tflops_megatron,
+    )
+
+    assert HardwareType.from_name("NVIDIA B200") is HardwareType.B200
+    assert HardwareType.from_name("NVIDIA A100-SXM4-80GB") is HardwareType.A100
+    assert HardwareType.from_name("NVIDIA H100 80GB HBM3") is HardwareType.H100
+    assert HardwareType.from_name("Tesla K80") is HardwareType.DEFAULT
+    assert HardwareType.B200.max_tflops == 2250e12
+    from scaling_b200.models import architecture_preset
+
+    a = TransformerArchitectureConfig.from_dict(architecture_preset("mistral_7b"))
+    topo = Topology(TopologyConfig(model_parallel_size=1, pipe_parallel_size=1, data_parallel_size=1, micro_batch_size=1,
+                                   gradient_accumulation_steps=8, global_rank=0))
+    n = 7.24e9
+    vals = [get_tflops_megatron(int(n), 1.66, topo, a), get_tflops_aleph_alpha(1.66, topo, a), get_tflops_bloom(1.66, topo, a),
+            get_tflops_electra(1.66, topo, a)]
+    # the measured N=1 step (1.66 s): ~0.9 PFLOP/s by the architecture-aware estimators; the parameter-count based
+    # "megatron" estimator (kept formula-identical to the reference) counts 60·s²·h·L for attention and reads higher
+    assert all(850 < v < 960 for v in vals[1:]) and 1300 < vals[0] < 1700, vals
+    mfu = get_model_flop_utilization_palm(1.66, int(n), topo, a, peak_flops=2250e12)
+    assert 0.3 < mfu < 0.5
+    assert get_tflops_megatron(int(n), 0.83, topo, a) == pytest.approx(2 * vals[0])
+
+
+# ------------------------------------------------------------------------- inference module == training module
+def _consistency_worker(rank: int, world_size: int, master_port: int, ckpt: str):
+    from scaling_b200.core import LaunchConfig
+    from scaling_b200.transformer.train import build_trainer
+    from tests.transformer_utils import tiny_config
+
+    cfg = tiny_config(Path(ckpt) / "data" / "tokens", iters=2, trainer={"save_dir": str(Path(ckpt) / "ck"), "save_interval": 2})
+    launch = LaunchConfig(master_port=master_port, master_addr="127.0.0.1", world_size=1, global_rank=0, local_slot=0, payload=cfg)
+    trainer = build_trainer(launch)
+    trainer.run_training()
+    from scaling_b200.transformer.data import TextDatasetBatch
+
+    ids = torch.tensor([[5, 16, 49, 21, 64, 3, 10, 31]])
+    trainer.parallel_module.eval()
+    with torch.no_grad():
+        x = TextDatasetBatch(input_token_ids=ids)
+        for _, layer in trainer.parallel_module.local_layers():
+            x = layer(x)
+    return x.activations.float().cpu()
+
+
+def test_inference_module_matches_training_module(tmp_path):
+    from scaling_b200.transformer.inference import TransformerInferenceModule
+    from tests.test_inference_cpu import _vocab_file
+    from tests.transformer_utils import write_dataset
+
+    write_dataset(tmp_path / "data" / "tokens")
+    trained = dist_launcher(_consistency_worker, 1, ckpt=str(tmp_path))[0]
+    step_dir = tmp_path / "ck" / "global_step2"
+    _vocab_file(step_dir / "vocab.json")
+    model = TransformerInferenceModule.from_checkpoint(step_dir, devices=["cpu"])
+    logits = model.logits(input_tokens=[5, 16, 49, 21, 64, 3, 10, 31])
+    assert torch.allclose(logits.float(), trained.squeeze(0), atol=1e-5)

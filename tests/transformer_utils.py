@@ -39,7 +39,8 @@ def tiny_config(data_prefix: Path, mp: int = 1, pp: int = 1, dp: int = 1, gas: i
         "topology": {"model_parallel_size": mp, "pipe_parallel_size": pp, "data_parallel_size": dp, "micro_batch_size": 2,
                      "gradient_accumulation_steps": gas, **over.pop("topology", {})},
         "optimizer": {"zero": True, "gradient_clipping": 1.0, **over.pop("optimizer", {})},
-        "learning_rate_scheduler": {"learning_rate": 0.01, "learning_rate_decay_style": "constant"},
+        "learning_rate_scheduler": {"learning_rate": 0.01, "learning_rate_decay_style": "constant",
+                                    **over.pop("learning_rate_scheduler", {})},
         "training": {"weight_decay": 0.01, **over.pop("training", {})},
         "trainer": {"train_iterations": iters, "assert_checkpoint_loaded": False, "seed": 42,
                     "dataloader_pin_memory": False, "delete_past_optimizer_states": False, **over.pop("trainer", {})},
