@@ -18,6 +18,8 @@
 //   warps 4..7    softmax of tile a, warps 8..11 softmax of tile b (one query row per thread): two passes over the S
 //                 row in TMEM (max, then exp2 + sum + bf16 pack), lazy rescale of O in TMEM only when the row max grew
 //                 by more than 2^8, final O/l and LSE
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace sb {
@@ -542,10 +544,8 @@ SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_l
     tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS^T over the consumed dP^T columns
   }
 }
-__global__ void __launch_bounds__(384, 1)
-attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
-                          const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
-                          const BwdParams p) {
+SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do, const CUtensorMap& map_k,
+                             const CUtensorMap& map_v, const BwdParams& p, const int kv_tile, const int kv_head) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sK = smem;
@@ -556,8 +556,8 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap map_q, const __gri
   BwdBarriers* bars = reinterpret_cast<BwdBarriers*>(sub_mask + kMaxSubs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kv0 = blockIdx.x * 128;
-  const int kvh = blockIdx.y;
+  const int kv0 = kv_tile * 128;
+  const int kvh = kv_head;
   const int group = p.heads / p.kv_heads;
   const int kv_last = min(kv0 + 128, p.T) - 1;
   // queries that can see a key of this tile: same sequence(s), and not before the key when causal
@@ -732,10 +732,8 @@ SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, in
     tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS over the consumed dP columns
   }
 }
-__global__ void __launch_bounds__(384, 1)
-attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
-                        const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
-                        const BwdParams p) {
+SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, const CUtensorMap& map_k,
+                           const CUtensorMap& map_v, const BwdParams& p, const int q_tile, const int q_head) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
@@ -744,8 +742,8 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_
   BwdBarriers* bars = reinterpret_cast<BwdBarriers*>(ring + kRing * 2 * kSubBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = (gridDim.x - 1 - blockIdx.x) * 128;
-  const int head = blockIdx.y;
+  const int q0 = q_tile * 128;
+  const int head = q_head;
   const int kvh = head / (p.heads / p.kv_heads);
   const int q_last = min(q0 + 128, p.T) - 1;
   const int kv_begin = (p.seg_start[q0] / BS) * BS;
@@ -893,6 +891,27 @@ static int make_map_box(CUtensorMap* m, const void* ptr, uint64_t width, uint64_
              : -2;
 }
 
+// One launch for the whole backward: blocks [0, n_dkdv) compute dK/dV of one (key tile, kv head), blocks
+// [n_dkdv, n_dkdv + n_dq) compute dQ of one (query tile, head).  Both sets are ordered heaviest first (causal: early key
+// tiles / late query tiles see the most partners), so the block scheduler packs the light dQ tiles into the holes the
+// long dK/dV tiles leave — with few heads per GPU (tensor parallel) the dK/dV grid alone is a single, badly balanced wave.
+__global__ void __launch_bounds__(384, 1)
+attention_bwd_kernel(const __grid_constant__ CUtensorMap kv_map_q, const __grid_constant__ CUtensorMap kv_map_do,
+                     const __grid_constant__ CUtensorMap kv_map_k, const __grid_constant__ CUtensorMap kv_map_v,
+                     const __grid_constant__ CUtensorMap q_map_q, const __grid_constant__ CUtensorMap q_map_do,
+                     const __grid_constant__ CUtensorMap q_map_k, const __grid_constant__ CUtensorMap q_map_v,
+                     const BwdParams p, const int first_block) {
+  const int b = (int)blockIdx.x + first_block;
+  const int tiles = (p.T + 127) / 128;
+  const int n_dkdv = tiles * p.kv_heads;
+  if (b < n_dkdv) {
+    bwd_dkdv_body(kv_map_q, kv_map_do, kv_map_k, kv_map_v, p, b / p.kv_heads, b % p.kv_heads);
+  } else {
+    const int c = b - n_dkdv;
+    bwd_dq_body(q_map_q, q_map_do, q_map_k, q_map_v, p, tiles - 1 - c / p.heads, c % p.heads);
+  }
+}
+
 }  // namespace attn
 }  // namespace sb
 
@@ -924,28 +943,30 @@ extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, 
   p.seg_start = seg_start, p.seg_end = seg_end, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
   p.dq = (__nv_bfloat16*)dq, p.dk = (__nv_bfloat16*)dk, p.dv = (__nv_bfloat16*)dv;
   static bool configured = false;
+  static bool separate = false;  // SCALING_B200_ATTN_BWD_SEPARATE=1: two launches (dK/dV, then dQ), for A/B timing
   if (!configured) {
-    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
-    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
+    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
+    const char* e = getenv("SCALING_B200_ATTN_BWD_SEPARATE");
+    separate = e && e[0] == '1';
     configured = true;
   }
-  {  // dK, dV: K/V tiles are stationary (128-row boxes), Q/dO streamed (64-row boxes)
-    CUtensorMap mq, mdo, mk, mv;
-    if (make_map_box(&mq, q, (uint64_t)heads * D, T, q_pitch, BS)) return -2;
-    if (make_map_box(&mdo, dout, (uint64_t)heads * D, T, (uint64_t)heads * D, BS)) return -2;
-    if (make_map_box(&mk, k, (uint64_t)kv_heads * D, T, k_pitch, 128)) return -2;
-    if (make_map_box(&mv, v, (uint64_t)kv_heads * D, T, v_pitch, 128)) return -2;
-    dim3 grid((T + 127) / 128, kv_heads);
-    attention_bwd_dkdv_kernel<<<grid, 384, kBwdSmemBytes, stream>>>(mq, mdo, mk, mv, p);
-  }
-  {  // dQ: Q/dO tiles stationary, K/V streamed
-    CUtensorMap mq, mdo, mk, mv;
-    if (make_map_box(&mq, q, (uint64_t)heads * D, T, q_pitch, 128)) return -2;
-    if (make_map_box(&mdo, dout, (uint64_t)heads * D, T, (uint64_t)heads * D, 128)) return -2;
-    if (make_map_box(&mk, k, (uint64_t)kv_heads * D, T, k_pitch, BS)) return -2;
-    if (make_map_box(&mv, v, (uint64_t)kv_heads * D, T, v_pitch, BS)) return -2;
-    dim3 grid((T + 127) / 128, heads);
-    attention_bwd_dq_kernel<<<grid, 384, kBwdSmemBytes, stream>>>(mq, mdo, mk, mv, p);
+  // dK/dV blocks: K/V tiles stationary (128-row boxes), Q/dO streamed (64-row boxes); dQ blocks: the other way round
+  CUtensorMap kq, kdo, kk, kv_, qq, qdo, qk, qv;
+  if (make_map_box(&kq, q, (uint64_t)heads * D, T, q_pitch, BS)) return -2;
+  if (make_map_box(&kdo, dout, (uint64_t)heads * D, T, (uint64_t)heads * D, BS)) return -2;
+  if (make_map_box(&kk, k, (uint64_t)kv_heads * D, T, k_pitch, 128)) return -2;
+  if (make_map_box(&kv_, v, (uint64_t)kv_heads * D, T, v_pitch, 128)) return -2;
+  if (make_map_box(&qq, q, (uint64_t)heads * D, T, q_pitch, 128)) return -2;
+  if (make_map_box(&qdo, dout, (uint64_t)heads * D, T, (uint64_t)heads * D, 128)) return -2;
+  if (make_map_box(&qk, k, (uint64_t)kv_heads * D, T, k_pitch, BS)) return -2;
+  if (make_map_box(&qv, v, (uint64_t)kv_heads * D, T, v_pitch, BS)) return -2;
+  const int tiles = (T + 127) / 128;
+  const int n_dkdv = tiles * kv_heads, n_dq = tiles * heads;
+  if (separate) {
+    attention_bwd_kernel<<<n_dkdv, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
+    attention_bwd_kernel<<<n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, n_dkdv);
+  } else {
+    attention_bwd_kernel<<<n_dkdv + n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
   }
   return (int)cudaGetLastError();
 }

@@ -32,7 +32,7 @@ def timeit(fn, iters=10):
 
 
 out = []
-for (Tt, heads, kvh, causal) in [(4096, 32, 8, True), (8192, 32, 8, True), (16384, 16, 4, True), (4096, 32, 8, False)]:
+for (Tt, heads, kvh, causal) in [(4096, 32, 8, True), (4096, 16, 4, True), (8192, 32, 8, True), (16384, 16, 4, True), (4096, 32, 8, False)]:
     q = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
     k = torch.randn(Tt, kvh, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
     v = torch.randn(Tt, kvh, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
