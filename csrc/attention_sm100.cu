@@ -128,9 +128,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
   Barriers* bars = reinterpret_cast<Barriers*>(smem + kTileBytes * (2 + kKStages + kVStages));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // heaviest (latest) query tiles first: under a causal mask their KV loops are the longest
-  const int q0 = (gridDim.x - 1 - blockIdx.x) * (2 * BQ);
-  const int head = blockIdx.y;
+  // heaviest (latest) query tiles first, over ALL heads, then the next lighter tile of all heads, … : under a causal
+  // mask the KV loop length grows with the tile index, and longest-first keeps the last wave short
+  const int n_q_tiles = (p.T + 2 * BQ - 1) / (2 * BQ);
+  const int q0 = (n_q_tiles - 1 - (int)blockIdx.x / p.heads) * (2 * BQ);
+  const int head = (int)blockIdx.x % p.heads;
   const int kv_head = head / (p.heads / p.kv_heads);
   // KV range: from the start of the first row's sequence to the diagonal (causal) or to the end of the last row's
   // sequence (bidirectional); seg_start/seg_end are non-decreasing along the packed dimension
@@ -405,8 +407,8 @@ extern "C" int sb_attention_fwd(const void* q, const void* k, const void* v, voi
     SB_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     configured = true;
   }
-  dim3 grid((T + 2 * BQ - 1) / (2 * BQ), heads);
-  attention_fwd_kernel<<<grid, kThreads, kSmemBytes, stream>>>(mq, mk, mv, p);
+  const int blocks = (T + 2 * BQ - 1) / (2 * BQ) * heads;
+  attention_fwd_kernel<<<blocks, kThreads, kSmemBytes, stream>>>(mq, mk, mv, p);
   return (int)cudaGetLastError();
 }
 
