@@ -24,6 +24,46 @@ int sb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int M,
 int sb_gemm_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
                         int ldh, int ldpre, int max_ctas, cudaStream_t stream);
 
+/* 2-CTA (tcgen05 cta_group::2, 256x256 tiles) variants with the same contracts; the Python layer selects them for
+ * M >= 256 and N >= 128.  The last, partial wave of tiles is split along K when each part keeps >= 112 k-blocks
+ * (fp32 partials meet in a library-owned workspace; disable with SCALING_B200_GEMM_SPLITK=0).
+ * Reference counterpart: cuBLAS GEMM behind F.linear (core/nn/linear/column_parallel_linear.py:151). */
+int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
+                  int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas, cudaStream_t st);
+int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
+                         int ldh, int ldpre, int max_ctas, cudaStream_t st);
+
+/* Fused tensor-parallel GEMM + all-reduce over NVLink peer memory: D = sum over ranks of op(A)·op(B) (+ bias), bf16,
+ * bit-identical on every rank.  data_ptrs[r] / flag_ptrs[r]: rank r's symmetric workspace regions of this call's
+ * parity, as mapped into this process (host arrays of tp_size addresses); epoch: per-workspace call counter, equal on
+ * all ranks; slot_bytes >= sb_gemm2_allreduce_slot_bytes(M, N); flag_slot >= slot_bytes / 65536 u32 flags per sender.
+ * a_layout must be 0 (K-major).  Reference counterpart: GEMM followed by torch.distributed.all_reduce
+ * (core/nn/linear/row_parallel_linear.py:150-160; backward of copy_to_tensor_model_parallel_region, utils.py:20-60). */
+int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
+                            int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
+                            const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                            unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas, cudaStream_t st);
+long long sb_gemm2_allreduce_slot_bytes(int M, int N);
+
+/* Flash attention for packed (varlen) sequences, head_dim 128, bf16, GQA; tcgen05 + TMEM + TMA.
+ * q/out: [T, heads, 128] (row pitch q_pitch elements), k/v: [T, kv_heads, 128]; seg_start/seg_end: per token, the
+ * first token / one past the last token of its sequence; lse: [heads, T] fp32.
+ * Backward is ONE launch: dK/dV blocks and dQ blocks share the grid (heaviest first).
+ * Reference counterpart: flash_attn_varlen_func (core/nn/attention/attention.py:245-258). */
+int sb_attention_fwd(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                     const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
+                     long long v_pitch, float scale, int causal, cudaStream_t st);
+int sb_attention_bwd_pitch(int T);
+long long sb_attention_bwd_scratch_floats(int T, int heads);
+int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
+                     float* scratch, void* dq, void* dk, void* dv, const int* seg_start, const int* seg_end, int T,
+                     int heads, int kv_heads, long long q_pitch, long long k_pitch, long long v_pitch, float scale,
+                     int causal, cudaStream_t st);
+
+/* Bind `device`'s primary context to the calling thread (tensor-map encoding is a driver call and needs one; PyTorch's
+ * autograd worker threads set their device lazily). */
+int sb_bind_device(int device);
+
 /* ---- norms (csrc/norm.cu) — core/nn/norm/rms_norm.py:45-53, core/nn/norm/layernorm.py:72-79 ---- */
 int sb_norm_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
                 float* rstd, int rows, int cols, float eps, int rms, int dtype, cudaStream_t st);
