@@ -160,6 +160,17 @@ class ParallelSelfAttention(torch.nn.Module):
         if key_query_norm:
             self.norm_query = get_norm(norm_type, layernorm_config, self.head_dim, self._device, dtype, bitfit_bias_name)
             self.norm_key = get_norm(norm_type, layernorm_config, self.head_dim, self._device, dtype, bitfit_bias_name)
+            # one replicated weight per norm, but every TP rank applies it to ITS heads only: the gradient is a partial
+            # sum and must be all-reduced over the TP group before the step (the reference never does -> its replicas
+            # drift apart under TP)
+            if self.model_parallel_size > 1:
+                from .parameter_meta import CoreParameterMeta
+
+                for norm in (self.norm_query, self.norm_key):
+                    for prm in norm.parameters():
+                        meta = getattr(prm, "core_parameter_meta", None) or CoreParameterMeta.register_on_parameter(
+                            prm, is_model_parallel=False)
+                        meta.tp_grad_reduce = "always"  # type: ignore[attr-defined]
 
         self.dropout_attention_probs = dropout_attention_probs
         self.dropout = torch.nn.Dropout(dropout_attention_probs)

@@ -156,6 +156,9 @@ class VocabParallelEmbedding(torch.nn.Module):
                     mask[t - self.vocab_start_index] = 1
             self._grad_mask = mask
             self.weight.register_hook(lambda g: g * self._grad_mask.to(g.dtype))
+            # the row mask lives in an autograd hook, so this weight's gradient must travel through autograd instead
+            # of being accumulated straight into the optimizer's main-grad arena by the embedding backward kernel
+            self.weight._sb_no_main_grad = True
 
     def grad_mask(self) -> Optional[torch.Tensor]:
         """[V_local, 1] 0/1 mask of trainable rows (``finetunable_token_ids``), or None when all rows train."""

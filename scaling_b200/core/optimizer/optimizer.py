@@ -159,6 +159,19 @@ class Optimizer(BaseOptimizer):
         views = [v for g in self.parameter_groups for v in g.grad_views(needs)]
         if views:
             allreduce_no_retain(views, topo.model_parallel_group, self.config.allreduce_bucket_size)
+        # replicated KV projections (fewer KV heads than TP ranks): rank r holds head r // replicas, so the gradient is
+        # summed over the `replicas` consecutive ranks that share a head — gather over the TP group, add the own block
+        tp, rank = topo.config.model_parallel_size, topo.model_parallel_rank
+        for g in self.parameter_groups:
+            for p, o, m in zip(g.parameters_original, g.offsets, g.parameter_metas):
+                replicas = getattr(m, "kv_replicas", 1)
+                if replicas <= 1:
+                    continue
+                view = g.grad_arena[o:o + p.numel()]
+                gathered = torch.empty(tp * view.numel(), dtype=view.dtype, device=view.device)
+                dist.all_gather_into_tensor(gathered, view.contiguous(), group=topo.model_parallel_group)
+                first = (rank // replicas) * replicas
+                view.copy_(gathered.view(tp, -1)[first:first + replicas].sum(0))
 
     def step(self) -> OptimizerStepOutput:
         self.step_index += 1

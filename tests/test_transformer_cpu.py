@@ -49,3 +49,22 @@ def test_weight_tying_and_layernorm_bias_model(data):
         "relative_position_embedding_type": "rotary"})
     losses = dist_launcher(run_transformer, 2, config_dict=cfg)[0]
     assert losses[-1] < losses[0]
+
+
+@pytest.mark.parametrize("arch", [
+    {"attention_num_kv_heads": 1},  # true MQA: the single KV head is replicated on both TP ranks
+    {"attention_num_kv_heads": 2, "key_query_norm": True},  # per-head QK-norm weights are TP-replicated
+])
+def test_tp_replicated_parameters_follow_single_gpu_run(tmp_path, data, arch):
+    """Replicated-but-partially-used parameters (MQA K/V projections, QK-norm weights) need their gradients summed
+    over the TP ranks that share them; with that, TP=2 follows the TP=1 loss curve from the same checkpoint."""
+    ckpt = tmp_path / "ckpt"
+    dist_launcher(run_transformer, 1, config_dict=tiny_config(data, 1, 1, 1, iters=1, arch=arch,
+                                                              trainer={"save_dir": str(ckpt), "save_interval": 1}))
+    one = dist_launcher(run_transformer, 1, config_dict=tiny_config(data, 1, 1, 1, iters=6, arch=arch,
+                                                                    trainer={"load_dir": str(ckpt)}))[0]
+    two = dist_launcher(run_transformer, 2, config_dict=tiny_config(data, 2, 1, 1, iters=6, arch=arch,
+                                                                    trainer={"load_dir": str(ckpt)}))[0]
+    assert len(one) == len(two) == 5
+    for a, b in zip(one, two):
+        assert abs(a - b) / abs(a) < 2e-3, (one, two)
