@@ -250,6 +250,7 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
                    loss_function: Callable[..., Any], metrics_aggregation_fn: Optional[Callable] = None) -> TrainStepOutput:
         self.step_timer.start()
         self._layers.train()
+        self._set_comm_mode("train")
         self.pipe_buffer.reset()
         self.profiler.step()
         step_out = None
@@ -269,6 +270,7 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
                         metrics_aggregation_fn: Optional[Callable] = None) -> EvaluationStepOutput:
         self.step_timer.start()
         self._layers.eval()
+        self._set_comm_mode("eval")
         self.pipe_buffer.reset()
         with torch.no_grad():
             for ins in self.eval_instructions:
@@ -291,6 +293,11 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
         """Forget cached p2p metadata (next message re-negotiates shapes)."""
         for c in (self.communicator_in, self.communicator_out):
             c.reset_communication_meta()
+
+    def _set_comm_mode(self, mode: str) -> None:
+        for c in (self.communicator_in, self.communicator_out, self.communicator_loss_in, self.communicator_loss_out):
+            if c is not None:
+                c.set_mode(mode)
 
     def _drain(self) -> None:
         for c in (self.communicator_in, self.communicator_out, self.communicator_loss_in, self.communicator_loss_out):

@@ -48,13 +48,33 @@ class PipeCommunicator:
         self.use_continuous_recommunication = use_continuous_recommunication
         self.group = group
         self.byte_wire = local_device.type != "cuda"  # gloo: ship raw bytes, every dtype works
-        self._send_meta: Optional[CommunicationMetaBase] = None
-        self._recv_meta: Optional[CommunicationMetaBase] = None
+        # cached handshakes, one per mode: training and evaluation messages differ in their requires_grad flags (and
+        # possibly shapes), and every rank switches mode at the same step, so each mode negotiates once
+        self._metas: dict = {}
+        self.mode = "train"
         self._pending: List[Tuple[Any, torch.Tensor]] = []
 
+    @property
+    def _send_meta(self) -> Optional[CommunicationMetaBase]:
+        return self._metas.get((self.mode, "send"))
+
+    @_send_meta.setter
+    def _send_meta(self, value: Optional[CommunicationMetaBase]) -> None:
+        self._metas[(self.mode, "send")] = value
+
+    @property
+    def _recv_meta(self) -> Optional[CommunicationMetaBase]:
+        return self._metas.get((self.mode, "recv"))
+
+    @_recv_meta.setter
+    def _recv_meta(self, value: Optional[CommunicationMetaBase]) -> None:
+        self._metas[(self.mode, "recv")] = value
+
+    def set_mode(self, mode: str) -> None:
+        self.mode = mode
+
     def reset_communication_meta(self) -> None:
-        self._send_meta = None
-        self._recv_meta = None
+        self._metas.clear()
 
     # ---- low level ----------------------------------------------------------------------------------
     def drain(self) -> None:

@@ -91,3 +91,88 @@ def _mp_comm_worker(rank: int, world_size: int, master_port: int):
 
 def test_model_parallel_communicator():
     assert all(dist_launcher(_mp_comm_worker, 2).values())
+
+
+def _eval_worker(rank: int, world_size: int, master_port: int, pp: int):
+    """Evaluation runs gradient_accumulation_steps micro batches through the inference schedule under no_grad and
+    reports evaluation/* metrics every eval_interval steps; parameters are untouched by it."""
+    import torch
+
+    from scaling_b200.core import BaseTrainer, Optimizer, OptimizerParamGroup, OptimizerParamGroupConfig, ParallelModule, Topology
+    from tests.minimal import (
+        MinimalConfig,
+        MinimalContext,
+        MinimalDataset,
+        layer_specs,
+        loss_function,
+        metrics_aggregation_fn,
+    )
+
+    cfg = MinimalConfig.from_dict({
+        "topology": {"model_parallel_size": 1, "pipe_parallel_size": pp, "data_parallel_size": 1, "micro_batch_size": 2,
+                     "gradient_accumulation_steps": 2, "world_size": world_size, "global_rank": rank, "local_slot": rank},
+        "trainer": {"train_iterations": 4, "assert_checkpoint_loaded": False, "eval_interval": 2, "seed": 1,
+                    "dataloader_pin_memory": False}})
+    topo = Topology(cfg.topology)
+    ctx = MinimalContext(config=cfg, topology=topo)
+    ctx.initialize(master_addr="127.0.0.1", master_port=str(master_port), seed=1)
+    model = ParallelModule(layer_specs(cfg, topo), topology=topo, profiler_config=cfg.profiler)
+    named = model.named_parameters_with_meta()
+    opt = Optimizer(cfg.optimizer, [OptimizerParamGroup(named, OptimizerParamGroupConfig(
+        name="all", weight_decay=0.0, learning_rate_scheduler=cfg.learning_rate_scheduler))], topo)
+    data = MinimalDataset(seed=1) if topo.is_io_rank else None
+    evald = MinimalDataset(seed=2, n=64) if topo.is_io_rank else None
+    trainer = BaseTrainer(config=cfg.trainer, context=ctx, parallel_module=model, optimizer=opt, dataset=data,
+                          dataset_evaluation=evald, sync_batch_to_model_parallel=MinimalDataset.sync_batch_to_model_parallel,
+                          loss_function=loss_function, metrics_aggregation_fn=metrics_aggregation_fn)
+    before = [p.detach().clone() for p in model.parameters()]
+    out = trainer.eval_step()
+    assert all(torch.equal(a, b) for a, b in zip(before, model.parameters()))
+    assert all(p.grad is None or float(p.grad.abs().sum()) == 0.0 for p in model.parameters())
+    metrics = trainer.run_training(return_metrics=True)
+    return {"eval_loss": out.loss, "keys": [sorted(k for k in m if k.startswith("evaluation/")) for m in (metrics or [])],
+            "consumed_eval": ctx.consumed_samples_evaluation}
+
+
+@pytest.mark.parametrize("pp", [1, 2])
+def test_evaluation_step(pp):
+    res = dist_launcher(_eval_worker, pp, pp=pp)[0]
+    assert res["eval_loss"] > 0
+    assert [bool(k) for k in res["keys"]] == [False, True, False, True]
+    assert "evaluation/loss" in res["keys"][1]
+    assert res["consumed_eval"] == 3 * 4  # one explicit + two scheduled evaluations of global batch 4
+
+
+def test_non_distributed_mode_and_buffers_in_checkpoint(tmp_path):
+    """`context.initialize(distributed=False)` only sets the device; persistent buffers are part of the layer files."""
+    import torch
+
+    from scaling_b200.core import ParallelModule, Topology
+    from tests.minimal import Batch, MinimalConfig, MinimalContext, layer_specs
+
+    cfg = MinimalConfig.from_dict({"topology": {"model_parallel_size": 1, "pipe_parallel_size": 1, "data_parallel_size": 1,
+                                                "micro_batch_size": 2, "gradient_accumulation_steps": 1, "world_size": 1,
+                                                "global_rank": 0, "local_slot": 0}})
+    topo = Topology(cfg.topology)
+    ctx = MinimalContext(config=cfg, topology=topo)
+    ctx.initialize(master_addr="127.0.0.1", master_port="0", seed=3, distributed=False)
+    assert not torch.distributed.is_initialized() and not topo.is_distributed_initialized
+    model = ParallelModule(layer_specs(cfg, topo), topology=topo, profiler_config=cfg.profiler)
+    x = Batch(inputs=torch.randint(0, 32, (2, 8)))
+    for _, layer in model.local_layers():
+        x = layer(x)
+    assert x.activations.shape == (2, 8, 32)
+    for _, layer in model.local_layers():
+        if hasattr(layer, "buffer_for_testing"):
+            layer.buffer_for_testing.fill_(7.0)
+    model.save_checkpoint(tmp_path)
+    files = sorted(p.name for p in tmp_path.glob("model_state_layer_*.pt"))
+    assert files == ["model_state_layer_0_EmbeddingLayer.pt", "model_state_layer_1_HiddenLayer.pt",
+                     "model_state_layer_2_HiddenLayer.pt", "model_state_layer_3_HeadLayer.pt"]
+    sd = torch.load(tmp_path / files[1], weights_only=False)
+    assert "buffer_for_testing" in sd and float(sd["buffer_for_testing"][0]) == 7.0
+    fresh = ParallelModule(layer_specs(cfg, topo), topology=topo, profiler_config=cfg.profiler)
+    fresh.load_checkpoint(tmp_path)
+    for (_, a), (_, b) in zip(model.local_layers(), fresh.local_layers()):
+        for (n1, t1), (n2, t2) in zip(a.state_dict().items(), b.state_dict().items()):
+            assert n1 == n2 and torch.equal(t1, t2), n1
