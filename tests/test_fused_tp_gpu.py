@@ -112,14 +112,44 @@ def _train_worker(rank: int, world_size: int, master_port: int, config_dict, fus
     return [m["training/loss"] for m in (metrics or [])]
 
 
-def test_tp2_training_fused_matches_nccl(tmp_path):
+@pytest.mark.parametrize("arch", [
+    {"num_attention_heads": 4, "attention_num_kv_heads": 2},
+    # GPT-style: biases (added once, after the fused reduction), fused qkv, GELU MLP, LayerNorm, tied LM head
+    {"num_attention_heads": 4, "attention_num_kv_heads": None, "attention_qkv_in_one": True, "norm_type": "layernorm",
+     "mlp_type": "default", "mlp_factor": 4.0, "attention_bias": True, "mlp_bias": True, "weight_tying": True,
+     "relative_position_embedding_type": "rotary"},
+])
+def test_tp2_training_fused_matches_nccl(tmp_path, arch):
     prefix = tmp_path / "d" / "tokens"
     write_dataset(prefix, n_docs=512, vocab=512)
-    arch = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
-            "sequence_length": 256, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"}}
-    cfg = tiny_config(prefix, mp=2, iters=5, gas=2, arch=arch)
+    a = {"vocab_size": 512, "hidden_size": 512, "sequence_length": 256, "precision": "bfloat16",
+         "masked_softmax": {"kernel": "flash_attention"}}
+    a.update(arch)
+    cfg = tiny_config(prefix, mp=2, iters=5, gas=2, arch=a)
     fused = dist_launcher(_train_worker, world_size=2, timeout=400, config_dict=cfg, fused=True)[0]
     plain = dist_launcher(_train_worker, world_size=2, timeout=400, config_dict=cfg, fused=False)[0]
     assert len(fused) == 5 and all(x == x for x in fused)
     for x, y in zip(fused, plain):
         assert abs(x - y) / abs(y) < 2e-2, (fused, plain)
+
+
+def _pp_tp_worker(rank: int, world_size: int, master_port: int, config_dict):
+    from scaling_b200.core import LaunchConfig
+    from scaling_b200.transformer.train import main
+
+    launch = LaunchConfig(master_port=master_port, master_addr="127.0.0.1", world_size=world_size, global_rank=rank,
+                          local_slot=rank, payload=config_dict)
+    metrics = main(launch, return_metrics=True)
+    return [m["training/loss"] for m in (metrics or [])]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+def test_tp2_pp2_training_on_nccl(tmp_path):
+    """The headline layout in small: tensor x pipeline parallel with the fused collectives, evaluation in between."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=512, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
+         "sequence_length": 256, "precision": "bfloat16", "num_layers": 4, "masked_softmax": {"kernel": "flash_attention"}}
+    cfg = tiny_config(prefix, mp=2, pp=2, iters=6, gas=4, arch=a)
+    losses = dist_launcher(_pp_tp_worker, world_size=4, timeout=400, config_dict=cfg)[0]
+    assert len(losses) == 6 and all(x == x for x in losses) and losses[-1] < losses[0]
