@@ -111,9 +111,17 @@ struct V4<__half> {
 // norm_sq: device scalar with the *global* Σg² of the still-scaled gradients (may be null when clip == 0).
 // skip: device flag, non-zero -> leave everything untouched (overflow step).
 // Four elements per thread with 128-bit accesses on the fp32 streams; a scalar tail handles n % 4.
+// `outs`: where the updated model-dtype values go — the rank's own parameter arena and, under fused ZeRO, the same
+// offset of every data-parallel peer's arena (peer-mapped pointers: the all-gather is these stores).
+constexpr int kMaxPeers = 8;
+template <typename P>
+struct OutPtrs {
+  P* p[kMaxPeers];
+  int n;
+};
 template <typename G, typename P>
 __global__ void __launch_bounds__(kThreads) adamw_kernel(float* __restrict__ p32, float* __restrict__ m,
-                                                         float* __restrict__ v, G* __restrict__ g, P* __restrict__ out,
+                                                         float* __restrict__ v, G* __restrict__ g, OutPtrs<P> outs,
                                                          size_t n, AdamArgs a, const float* __restrict__ norm_sq,
                                                          const int* __restrict__ skip) {
   if (skip && *skip) return;
@@ -146,7 +154,7 @@ __global__ void __launch_bounds__(kThreads) adamw_kernel(float* __restrict__ p32
     V4<float>::store(m + e, mv);
     V4<float>::store(v + e, vv);
     V4<float>::store(p32 + e, pv);
-    if (out) V4<P>::store(out + e, pv);
+    for (int r = 0; r < outs.n; ++r) V4<P>::store(outs.p[r] + e, pv);
     if (a.zero_grad) V4<G>::store(g + e, gv);
   }
   if (blockIdx.x == 0) {
@@ -155,8 +163,38 @@ __global__ void __launch_bounds__(kThreads) adamw_kernel(float* __restrict__ p32
       float mi = a.beta1 * m[i] + om1 * grad, vi = a.beta2 * v[i] + om2 * grad * grad;
       float pi = p32[i] * decay - step_size * mi / (sqrtf(vi) * inv_bc2 + a.eps);
       m[i] = mi, v[i] = vi, p32[i] = pi;
-      if (out) out[i] = (P)pi;
+      for (int r = 0; r < outs.n; ++r) outs.p[r][i] = (P)pi;
       if (a.zero_grad) g[i] = (G)0.f;
+    }
+  }
+}
+
+// Fused ZeRO reduce-scatter: own[i] = Σ_r peer_r[i] over this rank's shard, read straight from the data-parallel peers'
+// gradient arenas over NVLink (peer-mapped pointers), summed in rank order (identical bits wherever it is computed).
+template <typename G>
+struct InPtrs {
+  const G* p[kMaxPeers];
+  int n;
+};
+template <typename G>
+__global__ void __launch_bounds__(kThreads) peer_reduce_kernel(InPtrs<G> ins, G* __restrict__ own, size_t n) {
+  const size_t n4 = n / 4;
+  for (size_t i = blockIdx.x * (size_t)kThreads + threadIdx.x; i < n4; i += (size_t)gridDim.x * kThreads) {
+    const size_t e = i * 4;
+    float acc[4], x[4];
+    V4<G>::load(ins.p[0] + e, acc);
+    for (int r = 1; r < ins.n; ++r) {
+      V4<G>::load(ins.p[r] + e, x);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc[k] += x[k];
+    }
+    V4<G>::store(own + e, acc);
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = n4 * 4 + threadIdx.x; i < n; i += kThreads) {
+      float acc = (float)ins.p[0][i];
+      for (int r = 1; r < ins.n; ++r) acc += (float)ins.p[r][i];
+      own[i] = (G)acc;
     }
   }
 }
@@ -198,12 +236,12 @@ extern "C" int sb_grad_sumsq(const void* g, long long n, int dtype, float* scrat
   return (int)cudaGetLastError();
 }
 
-// grad_dtype / out_dtype: 0 bf16, 1 fp32, 2 fp16 (out may be null)
-extern "C" int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long long n, int grad_dtype, int out_dtype,
-                        float lr, float beta1, float beta2, float eps, float weight_decay, int step,
-                        float inv_loss_scale, float clip, const float* norm_sq, const int* skip, int zero_grad,
-                        cudaStream_t st) {
+static int adamw_impl(float* p32, float* m, float* v, void* g, void* out, const unsigned long long* peer_outs,
+                      int n_peer_outs, long long n, int grad_dtype, int out_dtype, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, int step, float inv_loss_scale, float clip, const float* norm_sq,
+                      const int* skip, int zero_grad, cudaStream_t st) {
   if (n <= 0) return 0;
+  if (n_peer_outs > kMaxPeers) return -5;
   AdamArgs a;
   a.lr = lr, a.beta1 = beta1, a.beta2 = beta2, a.eps = eps, a.weight_decay = weight_decay;
   a.bias_corr1 = 1.f - powf(beta1, (float)step);
@@ -212,8 +250,16 @@ extern "C" int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long
   // the vector path needs 16-byte aligned shards (arena shards are 128-element aligned)
   if (((uintptr_t)p32 | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g | (uintptr_t)out) & 15) return -4;
   const int b = blocks((size_t)n / 4 + 1);
-#define SB_ADAM(GT, PT) \
-  adamw_kernel<GT, PT><<<b, kThreads, 0, st>>>(p32, m, v, (GT*)g, (PT*)out, (size_t)n, a, norm_sq, skip)
+#define SB_ADAM(GT, PT)                                                                                   \
+  do {                                                                                                    \
+    OutPtrs<PT> o{};                                                                                      \
+    o.n = 0;                                                                                              \
+    if (n_peer_outs > 0)                                                                                  \
+      for (int r = 0; r < n_peer_outs; ++r) o.p[o.n++] = (PT*)peer_outs[r];                                \
+    else if (out)                                                                                         \
+      o.p[o.n++] = (PT*)out;                                                                              \
+    adamw_kernel<GT, PT><<<b, kThreads, 0, st>>>(p32, m, v, (GT*)g, o, (size_t)n, a, norm_sq, skip);      \
+  } while (0)
   if (grad_dtype == 0 && out_dtype == 0) SB_ADAM(__nv_bfloat16, __nv_bfloat16);
   else if (grad_dtype == 1 && out_dtype == 0) SB_ADAM(float, __nv_bfloat16);
   else if (grad_dtype == 1 && out_dtype == 1) SB_ADAM(float, float);
@@ -222,6 +268,53 @@ extern "C" int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long
   else if (grad_dtype == 1 && out_dtype == 2) SB_ADAM(float, __half);
   else return -2;
 #undef SB_ADAM
+  return (int)cudaGetLastError();
+}
+
+// grad_dtype / out_dtype: 0 bf16, 1 fp32, 2 fp16 (out may be null)
+extern "C" int sb_adamw(float* p32, float* m, float* v, void* g, void* out, long long n, int grad_dtype, int out_dtype,
+                        float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                        float inv_loss_scale, float clip, const float* norm_sq, const int* skip, int zero_grad,
+                        cudaStream_t st) {
+  return adamw_impl(p32, m, v, g, out, nullptr, 0, n, grad_dtype, out_dtype, lr, beta1, beta2, eps, weight_decay, step,
+                    inv_loss_scale, clip, norm_sq, skip, zero_grad, st);
+}
+
+// Fused ZeRO-1 step, second half: AdamW on this rank's shard, and the updated model-dtype values are stored to the
+// shard's offset in EVERY data-parallel rank's parameter arena (`peer_outs`: dp peer-mapped addresses, own included) —
+// the parameter all-gather is the kernel's own stores over NVLink.  Reference: AdamW then all_gather
+// (core/optimizer/parameter_group.py:423-481).
+extern "C" int sb_adamw_zero(float* p32, float* m, float* v, void* g, const unsigned long long* peer_outs, int n_peers,
+                             long long n, int grad_dtype, int out_dtype, float lr, float beta1, float beta2, float eps,
+                             float weight_decay, int step, float inv_loss_scale, float clip, const float* norm_sq,
+                             const int* skip, int zero_grad, cudaStream_t st) {
+  if (n_peers < 1) return -5;
+  return adamw_impl(p32, m, v, g, nullptr, peer_outs, n_peers, n, grad_dtype, out_dtype, lr, beta1, beta2, eps,
+                    weight_decay, step, inv_loss_scale, clip, norm_sq, skip, zero_grad, st);
+}
+
+// Fused ZeRO-1 step, first half: own[i] = Σ_r peers[r][i] for this rank's gradient shard; `peer_grads` are the dp
+// peer-mapped addresses of the shard inside every rank's gradient arena, in rank order (own included).  The
+// reduce-scatter is the kernel's own loads over NVLink.  Reference: all-reduce then slice
+// (core/optimizer/parameter_group.py:346-394, allreduce.py).
+extern "C" int sb_zero_reduce(const unsigned long long* peer_grads, int n_peers, void* own, long long n, int grad_dtype,
+                              cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n_peers < 1 || n_peers > kMaxPeers) return -5;
+  const int b = blocks((size_t)n / 4 + 1);
+  if (grad_dtype == 1) {
+    InPtrs<float> in{};
+    in.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) in.p[r] = (const float*)peer_grads[r];
+    peer_reduce_kernel<float><<<b, kThreads, 0, st>>>(in, (float*)own, (size_t)n);
+  } else if (grad_dtype == 0) {
+    InPtrs<__nv_bfloat16> in{};
+    in.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) in.p[r] = (const __nv_bfloat16*)peer_grads[r];
+    peer_reduce_kernel<__nv_bfloat16><<<b, kThreads, 0, st>>>(in, (__nv_bfloat16*)own, (size_t)n);
+  } else {
+    return -2;
+  }
   return (int)cudaGetLastError();
 }
 

@@ -3,8 +3,8 @@ core/nn/parallel_module/activation_checkpointing.py:1-190).
 
 Non-reentrant: ``saved_tensors_hooks`` replace every tensor autograd wants to save by a slot; at the first unpack the
 forward is replayed once with the device RNG *and* the tensor-parallel-constant RNG restored to their values at the
-original forward, and the slots are filled in order.  The Philox dropout kernels need no RNG handling at all — their
-mask depends only on (seed, offset) carried in the layer IO.
+original forward, and the slots are filled in order.  The Philox dropout kernels carry no RNG state — their mask
+depends only on (seed, offset); the replay restores the topology's offset counter so the same ranges are drawn.
 """
 from __future__ import annotations
 
@@ -24,6 +24,8 @@ def _rng_snapshot(topology: Any, device: Optional[torch.device]) -> Dict[str, An
         snap["cuda"] = torch.cuda.get_rng_state(device)
     if topology is not None and topology.has_model_parallel_constant_rng():
         snap["mp"] = topology._rng.state.clone()
+    if topology is not None and hasattr(topology, "dropout_offset"):
+        snap["dropout_offset"] = topology.dropout_offset  # Philox dropout: replay the same counter ranges
     return snap
 
 
@@ -33,6 +35,8 @@ def _rng_restore(snap: Dict[str, Any], topology: Any, device: Optional[torch.dev
         torch.cuda.set_rng_state(snap["cuda"], device)
     if "mp" in snap:
         topology._rng.state = snap["mp"].clone()
+    if "dropout_offset" in snap:
+        topology.dropout_offset = snap["dropout_offset"]
 
 
 def _checkpoint_without_reentrant(function: Callable[..., Any], topology: Any, *args: Any) -> Any:

@@ -110,8 +110,22 @@ class OptimizerParamGroup:
         self.counted_end = off if counted_end is None else counted_end
         dp = topology.config.data_parallel_size if self.zero else 1
         self.total = _round_up(max(off, ALIGN), ALIGN * dp)
-        self.param_arena = torch.zeros(self.total, dtype=self.model_dtype, device=device)
-        self.grad_arena = torch.zeros(self.total, dtype=self.grad_dtype, device=device)
+        self._sym_params = self._sym_grads = None
+        if self.zero:
+            from ...parallel.symm import SymmetricArena, fused_zero_enabled
+
+            if fused_zero_enabled(topology) and self.grad_dtype in native.DTYPE_CODE and self.model_dtype in native.DTYPE_CODE:
+                # arenas every DP rank can address: the reduce-scatter becomes peer loads inside the reduce kernel and
+                # the all-gather peer stores inside the AdamW kernel (collective: all DP ranks build their groups in
+                # the same order)
+                self._sym_params = SymmetricArena(self.total, self.model_dtype, topology.data_parallel_group, device)
+                self._sym_grads = SymmetricArena(self.total, self.grad_dtype, topology.data_parallel_group, device)
+        if self._sym_params is not None:
+            self.param_arena = self._sym_params.tensor
+            self.grad_arena = self._sym_grads.tensor
+        else:
+            self.param_arena = torch.zeros(self.total, dtype=self.model_dtype, device=device)
+            self.grad_arena = torch.zeros(self.total, dtype=self.grad_dtype, device=device)
         for p, o in zip(self.parameters_original, self.offsets):
             n = p.numel()
             view = self.param_arena[o:o + n].view(p.shape)
@@ -172,7 +186,12 @@ class OptimizerParamGroup:
         topo = self.topology
         if topo.config.data_parallel_size == 1 or not topo.is_distributed_initialized:
             return
-        if self.zero and topo.backend == "nccl":
+        if self._sym_grads is not None:
+            n = self.shard_end - self.shard_start
+            self._sym_grads.barrier()  # every rank's backward (its writes to its own arena) is complete
+            native.call("sb_zero_reduce", self._sym_grads.ptr_array(self.shard_start), self._sym_grads.world,
+                        native.ptr(self.grad_shard), n, native.DTYPE_CODE[self.grad_dtype])
+        elif self.zero and topo.backend == "nccl":
             dist.reduce_scatter_tensor(self.grad_shard, self.grad_arena, group=topo.data_parallel_group)
         else:
             dist.all_reduce(self.grad_arena, group=topo.data_parallel_group)
@@ -198,6 +217,16 @@ class OptimizerParamGroup:
                     norm_sq: Optional[torch.Tensor], skip: Optional[torch.Tensor]) -> None:
         self._lr = self.learning_rate_scheduler.get_lr(step_index)
         wd = self.config.weight_decay
+        if self._sym_params is not None:
+            import math
+
+            n = self.shard_end - self.shard_start
+            native.call("sb_adamw_zero", native.ptr(self.master), native.ptr(self.exp_avg), native.ptr(self.exp_avg_sq),
+                        native.ptr(self.grad_shard), self._sym_params.ptr_array(self.shard_start), self._sym_params.world, n,
+                        native.DTYPE_CODE[self.grad_dtype], native.DTYPE_CODE[self.model_dtype], float(self._lr), float(beta1),
+                        float(beta2), float(eps), float(wd), int(step_index), float(inv_scale), float(clip),
+                        native.ptr(norm_sq), native.ptr(skip), 1)
+            return
         if self._use_native:
             K.adamw_step(self.master, self.exp_avg, self.exp_avg_sq, self.grad_shard, self.param_shard, lr=self._lr,
                          beta1=beta1, beta2=beta2, eps=eps, weight_decay=wd, step=step_index,
@@ -238,6 +267,11 @@ class OptimizerParamGroup:
         """ZeRO: all-gather the updated model-dtype shards in place (the cast happened inside the AdamW kernel)."""
         topo = self.topology
         if not self.zero or not topo.is_distributed_initialized:
+            return
+        if self._sym_params is not None:
+            # the AdamW kernels already stored every shard into every arena; wait until the peers' stores have landed
+            # here (and until nobody reads this rank's gradient arena any more)
+            self._sym_params.barrier()
             return
         if topo.backend == "nccl":
             dist.all_gather_into_tensor(self.param_arena, self.param_shard, group=topo.data_parallel_group)

@@ -160,6 +160,7 @@ class Topology:
         self._rng: Optional[CudaRNGStateTracker] = None
         self.is_distributed_initialized = False
         self.dropout_seed = 0
+        self.dropout_offset = 0  # Philox counter of the next dropout call; advances identically on all TP ranks
         self.backend: Optional[str] = None
 
     # ---- device / distributed init ---------------------------------------------------------------
@@ -222,10 +223,19 @@ class Topology:
             return contextlib.nullcontext()
         return self._rng.fork()
 
+    def next_dropout_offset(self, numel: int = 0) -> int:
+        """Stream id of the next Philox dropout call (the kernels hash (seed, element index, stream id), so every call
+        gets an independent mask).  TP ranks of one (pp, dp) cell share the seed and make the same calls in the same
+        order; activation recomputation replays the ids."""
+        off = self.dropout_offset
+        self.dropout_offset += 1
+        return off
+
     def state_dict(self) -> Optional[Dict[str, Any]]:
         if self._rng is None:
             return None
         return {
+            "dropout_offset": self.dropout_offset,
             "model_parallel_constant_rng": self._rng.state_dict(),
             "model_parallel_size": self.config.model_parallel_size,
             "pipe_parallel_size": self.config.pipe_parallel_size,
@@ -238,6 +248,7 @@ class Topology:
         if (state_dict.get("model_parallel_size") == self.config.model_parallel_size
                 and state_dict.get("pipe_parallel_size") == self.config.pipe_parallel_size):
             self._rng.load_state_dict(state_dict["model_parallel_constant_rng"])
+            self.dropout_offset = int(state_dict.get("dropout_offset", 0))
 
     # ---- coordinates -----------------------------------------------------------------------------
     @property

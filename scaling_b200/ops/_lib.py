@@ -48,6 +48,9 @@ _SIGS = {
     "sb_adamw": [P, P, P, P, P, c_longlong, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_float,
                  c_float, P, P, c_int, P],
     "sb_cast_from_fp32": [P, P, c_longlong, c_int, P],
+    "sb_adamw_zero": [P, P, P, P, P, c_int, c_longlong, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_int,
+                      c_float, c_float, P, P, c_int, P],
+    "sb_zero_reduce": [P, c_int, P, c_longlong, c_int, P],
 }
 _RET_LL = {
     "sb_norm_bwd_scratch_floats": [c_int, c_int, c_int],

@@ -106,6 +106,53 @@ class TPComm:
         return x
 
 
+_FUSED_ZERO = os.environ.get("SCALING_B200_FUSED_ZERO", "1") == "1"
+
+
+def set_fused_zero(enabled: bool) -> None:
+    global _FUSED_ZERO
+    _FUSED_ZERO = bool(enabled)
+
+
+def fused_zero_enabled(topology: Any) -> bool:
+    """ZeRO-1 reduce-scatter / all-gather as peer loads / stores inside the optimizer kernels: NCCL job on CUDA, 2..8
+    data-parallel ranks (one NVLink domain), native library present."""
+    if topology is None or not _FUSED_ZERO or not topology.is_distributed_initialized:
+        return False
+    dp = topology.config.data_parallel_size
+    return (2 <= dp <= 8 and topology.backend == "nccl" and topology.device.type == "cuda" and _lib.available())
+
+
+class SymmetricArena:
+    """A flat tensor whose storage every rank of ``group`` can address: ``peer_ptrs[r]`` is rank r's copy as mapped
+    into this process.  Used for the ZeRO parameter and gradient arenas."""
+
+    def __init__(self, numel: int, dtype: torch.dtype, group: Any, device: torch.device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        name = group.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(name)
+        except Exception:  # noqa: BLE001
+            pass
+        self._buf = symm_mem.empty(numel, dtype=dtype, device=device)
+        self._hdl = symm_mem.rendezvous(self._buf, name)
+        self._buf.zero_()
+        self.tensor = self._buf
+        self.peer_ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self.rank = self._hdl.rank
+        self.world = self._hdl.world_size
+        self.itemsize = self._buf.element_size()
+
+    def barrier(self) -> None:
+        """Device-side barrier over the group on the current stream."""
+        self._hdl.barrier()
+
+    def ptr_array(self, element_offset: int):
+        arr = ctypes.c_ulonglong * self.world
+        return arr(*[p + element_offset * self.itemsize for p in self.peer_ptrs])
+
+
 def get_tp_comm(topology: Any) -> Optional[TPComm]:
     """The fused-collective communicator of ``topology``'s TP group, or None when the fused path does not apply
     (single TP rank, sequence parallelism, CPU / gloo, disabled by SCALING_B200_FUSED_TP=0)."""

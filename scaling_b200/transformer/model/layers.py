@@ -102,6 +102,9 @@ def _dropout(x: torch.Tensor, p: float, training: bool, topology: Optional[Topol
     """Dropout whose mask is identical on every TP rank (drawn from the TP-constant RNG stream); free when p == 0."""
     if p <= 0.0 or not training:
         return x
+    if topology is not None and OF.native_enabled(x) and x.dtype == torch.bfloat16 and x.numel() % 4 == 0:
+        # counter-based (Philox) mask: no RNG state to fork, identical on all TP ranks and under recomputation
+        return OF.bias_dropout_add(x, None, None, p, True, topology.dropout_seed, topology.next_dropout_offset(x.numel()))
     if topology is not None:
         with topology.model_parallel_constant_rng():
             return torch.nn.functional.dropout(x, p=p, training=True)

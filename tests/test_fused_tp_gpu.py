@@ -153,3 +153,30 @@ def test_tp2_pp2_training_on_nccl(tmp_path):
     cfg = tiny_config(prefix, mp=2, pp=2, iters=6, gas=4, arch=a)
     losses = dist_launcher(_pp_tp_worker, world_size=4, timeout=400, config_dict=cfg)[0]
     assert len(losses) == 6 and all(x == x for x in losses) and losses[-1] < losses[0]
+
+
+def _zero_worker(rank: int, world_size: int, master_port: int, config_dict, fused: bool):
+    from scaling_b200.core import LaunchConfig
+    from scaling_b200.parallel import symm
+    from scaling_b200.transformer.train import main
+
+    symm.set_fused_zero(fused)
+    launch = LaunchConfig(master_port=master_port, master_addr="127.0.0.1", world_size=world_size, global_rank=rank,
+                          local_slot=rank, payload=config_dict)
+    metrics = main(launch, return_metrics=True)
+    return [(m["training/loss"], m["training/global_grad_norm"]) for m in (metrics or [])]
+
+
+def test_dp2_fused_zero_matches_nccl(tmp_path):
+    """ZeRO-1 with the reduce-scatter as peer loads (sb_zero_reduce) and the all-gather as peer stores
+    (sb_adamw_zero) against the NCCL reduce_scatter / all_gather path: two summands commute, so the runs agree bitwise."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=512, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 256, "num_attention_heads": 2, "attention_num_kv_heads": 1,
+         "sequence_length": 128, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"}}
+    cfg = tiny_config(prefix, dp=2, iters=6, gas=2, arch=a)
+    fused = dist_launcher(_zero_worker, world_size=2, timeout=400, config_dict=cfg, fused=True)[0]
+    plain = dist_launcher(_zero_worker, world_size=2, timeout=400, config_dict=cfg, fused=False)[0]
+    assert len(fused) == 6
+    assert fused == plain, (fused, plain)
+    assert fused[-1][0] < fused[0][0]

@@ -55,3 +55,22 @@ def test_smoke_entry():
     g.smoke()
     if torch.distributed.is_initialized():
         torch.distributed.destroy_process_group()
+
+
+def test_philox_dropout_is_exact_under_activation_checkpointing(tmp_path):
+    """Dropout masks come from the counter-based kernel: recomputing a layer replays the same stream ids, so training
+    with and without activation checkpointing gives identical losses; and dropout really is applied."""
+    from scaling_b200.core.utils.port import find_free_port
+
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=256, vocab=512)
+    a = {"vocab_size": 512, "sequence_length": 128, "precision": "bfloat16", "hidden_size": 256, "num_attention_heads": 2,
+         "attention_num_kv_heads": 1, "masked_softmax": {"kernel": "flash_attention"}, "dropout_after_attention": 0.1,
+         "dropout_after_mlp": 0.1, "dropout_embedding": 0.1}
+    plain = _losses(tiny_config(prefix, iters=4, gas=2, arch=a), "sm100", find_free_port())
+    ckpt = _losses(tiny_config(prefix, iters=4, gas=2, arch=a, topology={"activation_checkpointing_type": "every_layer"}),
+                   "sm100", find_free_port())
+    assert plain == ckpt, (plain, ckpt)
+    nodrop = _losses(tiny_config(prefix, iters=4, gas=2, arch=dict(a, dropout_after_attention=0.0, dropout_after_mlp=0.0,
+                                                                   dropout_embedding=0.0)), "sm100", find_free_port())
+    assert plain != nodrop
