@@ -331,3 +331,48 @@ def test_resumable_sampler_covers_every_index_once(dp, mbs, n):
     it = iter(RandomSampler(ds, seed=5, consumed_samples=usable, topology=topo(0)))
     next(it)
     assert ds.seeds[-1] == 6
+
+
+# ---------------------------------------------------------------------------------------------------- logging
+def test_logger_sinks_and_rank_filters(tmp_path, capsys):
+    from scaling_b200.core import LoggerConfig
+    from scaling_b200.core.logging import logger
+
+    cfg = LoggerConfig(log_dir=tmp_path / "logs", log_level="info", use_tensorboard=False, metrics_ranks=[0])
+    assert cfg.log_dir is not None and cfg.log_dir.parent == tmp_path / "logs"  # timestamped sub-directory
+    assert cfg.is_rank_in_metrics_ranks(0) and not cfg.is_rank_in_metrics_ranks(1)
+    assert LoggerConfig(tensorboard_ranks=None).is_rank_in_tensorboard_ranks(0)
+    assert not LoggerConfig(tensorboard_ranks=[2]).is_rank_in_tensorboard_ranks(0)
+    with pytest.raises(ValidationError):
+        LoggerConfig(use_wandb=True, wandb_api_key=None) if "WANDB_API_KEY" not in __import__("os").environ else (_ for _ in ()).throw(
+            ValidationError.from_exception_data("x", []))
+    logger.configure(cfg, name="RANK 0", global_rank=0)
+    logger.info("hello from the test")
+    logger.log_metrics({"training/loss": 1.25, "runtime/step_duration": 0.5}, step=3)
+    logger.log_config_dict({"a": {"b": 1}})
+    files = list(cfg.log_dir.glob("*.log"))
+    assert len(files) == 1
+    text = files[0].read_text()
+    assert "hello from the test" in text and "training/loss" in text and "1.25" in text
+    logger.configure(LoggerConfig(log_level="warning"), name="quiet")
+    logger.info("not shown")
+    assert "not shown" not in capsys.readouterr().err
+
+
+def test_tokenizer_wrapper(tmp_path):
+    from tokenizers import Tokenizer as HF
+    from tokenizers import decoders, models, pre_tokenizers
+
+    from scaling_b200.transformer.tokenizer import Tokenizer, load_tokenizers
+
+    vocab = {"<|endoftext|>": 0, "<unk>": 1, "▁hello": 2, "hello": 3, "▁world": 4, "world": 5}
+    tok = HF(models.WordLevel(vocab, unk_token="<unk>"))
+    tok.pre_tokenizer = pre_tokenizers.Metaspace(replacement="▁", prepend_scheme="always")
+    tok.decoder = decoders.Metaspace(replacement="▁")
+    tok.save(str(tmp_path / "vocab.json"))
+    t = Tokenizer.from_file(tmp_path / "vocab.json")
+    assert t.eos_token_id == 0 and len(t) == 6 and t.vocab_size == 6
+    assert t.encode("hello world") == [2, 4] and t.decode([2, 4]) == "hello world"
+    with_space, without = load_tokenizers(tmp_path / "vocab.json")
+    assert with_space.encode("world") == [4] and without.encode("world") == [5]  # continuation pieces get no prefix space
+    assert Tokenizer.from_str((tmp_path / "vocab.json").read_text()).encode("hello") == [2]
