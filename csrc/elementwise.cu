@@ -115,6 +115,85 @@ __global__ void rope_kernel(__nv_bfloat16* __restrict__ x, const float* __restri
   }
 }
 
+// ------------------------------------------------------------------ fused q|k|v split + rotary (one pass)
+// Up to three head segments (q, k, v) are copied from their inputs to their outputs, 16 bytes per thread; segments with
+// `rotate` get the rotary embedding (dir = +1) or its inverse (dir = -1) on the way.  Forward: inputs are slices of
+// the fused q|k|v GEMM output, outputs one contiguous [tokens, heads, d] buffer; backward: inputs are dq, dk, dv,
+// outputs slices of the fused dY buffer the dgrad / wgrad GEMMs consume — no clone, no cat, no second rope launch.
+struct RopeSeg {
+  const __nv_bfloat16* in;
+  __nv_bfloat16* out;
+  long long in_pitch, out_pitch;  // elements per token
+  int heads, rotate;
+};
+struct RopeSegs {
+  RopeSeg s[3];
+  int n, total_heads;
+};
+SB_DEVICE void rot_pairs_interleaved(float* v, const float* c, const float* s, float dir) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float a = v[2 * k], b = v[2 * k + 1], sn = dir * s[k];
+    v[2 * k] = a * c[k] - b * sn;
+    v[2 * k + 1] = a * sn + b * c[k];
+  }
+}
+__global__ void qkv_rope_kernel(RopeSegs segs, const float* __restrict__ cs, const float* __restrict__ sn,
+                                const int* __restrict__ pos, int tokens, int head_dim, int rot_dim, int seq, int mode,
+                                float dir) {
+  const int chunks = head_dim / 8;  // 16-byte chunks per head
+  const int half = rot_dim / 2, half_chunks = half / 8;
+  const size_t total = (size_t)tokens * segs.total_heads * chunks;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % chunks);
+    const size_t th = i / chunks;
+    int hd = (int)(th % segs.total_heads);
+    const int t = (int)(th / segs.total_heads);
+    int si = 0;
+    while (si < segs.n - 1 && hd >= segs.s[si].heads) hd -= segs.s[si++].heads;
+    const RopeSeg& sg = segs.s[si];
+    const __nv_bfloat16* src = sg.in + (size_t)t * sg.in_pitch + (size_t)hd * head_dim;
+    __nv_bfloat16* dst = sg.out + (size_t)t * sg.out_pitch + (size_t)hd * head_dim;
+    const int e0 = c * 8;
+    if (!sg.rotate || e0 >= rot_dim) {
+      *reinterpret_cast<uint4*>(dst + e0) = *reinterpret_cast<const uint4*>(src + e0);
+      continue;
+    }
+    const int p = pos ? pos[t] : (t % seq);
+    const float* cr = cs + (size_t)p * half;
+    const float* sr = sn + (size_t)p * half;
+    if (mode == 0) {  // interleaved pairs: elements (2j, 2j+1), frequencies e0/2 .. e0/2+3
+      const uint4 x = *reinterpret_cast<const uint4*>(src + e0);
+      float v[8];
+      float2 f;
+      f = unpack_bf16(x.x), v[0] = f.x, v[1] = f.y;
+      f = unpack_bf16(x.y), v[2] = f.x, v[3] = f.y;
+      f = unpack_bf16(x.z), v[4] = f.x, v[5] = f.y;
+      f = unpack_bf16(x.w), v[6] = f.x, v[7] = f.y;
+      const float4 c4 = *reinterpret_cast<const float4*>(cr + e0 / 2), s4 = *reinterpret_cast<const float4*>(sr + e0 / 2);
+      const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+      rot_pairs_interleaved(v, cc, ss, dir);
+      *reinterpret_cast<uint4*>(dst + e0) =
+          make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    } else {  // half rotation: element j pairs with j + half; the thread of the first half handles both chunks
+      if (c >= half_chunks) continue;
+      const uint4 xa = *reinterpret_cast<const uint4*>(src + e0), xb = *reinterpret_cast<const uint4*>(src + e0 + half);
+      const uint32_t wa[4] = {xa.x, xa.y, xa.z, xa.w}, wb[4] = {xb.x, xb.y, xb.z, xb.w};
+      uint32_t oa[4], ob[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 a = unpack_bf16(wa[k]), b = unpack_bf16(wb[k]);
+        const float c0 = cr[e0 + 2 * k], c1 = cr[e0 + 2 * k + 1];
+        const float s0 = dir * sr[e0 + 2 * k], s1 = dir * sr[e0 + 2 * k + 1];
+        oa[k] = pack_bf16(a.x * c0 - b.x * s0, a.y * c1 - b.y * s1);
+        ob[k] = pack_bf16(a.x * s0 + b.x * c0, a.y * s1 + b.y * c1);
+      }
+      *reinterpret_cast<uint4*>(dst + e0) = make_uint4(oa[0], oa[1], oa[2], oa[3]);
+      *reinterpret_cast<uint4*>(dst + e0 + half) = make_uint4(ob[0], ob[1], ob[2], ob[3]);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ bias + dropout + residual
 // out = residual + dropout(x + bias); mask derived from Philox(seed, element index) — nothing is stored
 __global__ void bias_dropout_add_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ bias,
@@ -250,6 +329,31 @@ extern "C" int sb_rope(void* x, const float* cos_t, const float* sin_t, const in
   rope_kernel<<<blocks_for((size_t)tokens * heads * (rot_dim / 2)), 256, 0, st>>>(
       (__nv_bfloat16*)x, cos_t, sin_t, pos, tokens, heads, head_dim, rot_dim, token_stride, seq, mode,
       backward ? -1.f : 1.f);
+  return (int)cudaGetLastError();
+}
+// Fused split + rotary over up to three head segments.  ins/outs/in_pitch/out_pitch/heads/rotate: host arrays of
+// `n_seg` entries (pointers as integers); every pointer 16-byte aligned, pitches multiples of 8 elements, head_dim and
+// rot_dim/2 multiples of 8.  Reference: RotaryEmbedding(Complex).forward after the q/k/v projections
+// (core/nn/attention/attention.py:560-600, rotary.py:68-203).
+extern "C" int sb_qkv_rope(const unsigned long long* ins, const unsigned long long* outs, const long long* in_pitch,
+                           const long long* out_pitch, const int* heads, const int* rotate, int n_seg,
+                           const float* cos_t, const float* sin_t, const int* pos, int tokens, int head_dim, int rot_dim,
+                           int seq, int mode, int backward, cudaStream_t st) {
+  if (tokens <= 0) return 0;
+  if (n_seg < 1 || n_seg > 3 || head_dim % 8 || (rot_dim / 2) % 8 || rot_dim > head_dim) return -1;
+  sb::ew::RopeSegs segs{};
+  segs.n = n_seg;
+  for (int i = 0; i < n_seg; ++i) {
+    if ((ins[i] | outs[i]) & 15 || in_pitch[i] % 8 || out_pitch[i] % 8) return -4;
+    segs.s[i].in = (const __nv_bfloat16*)ins[i];
+    segs.s[i].out = (__nv_bfloat16*)outs[i];
+    segs.s[i].in_pitch = in_pitch[i], segs.s[i].out_pitch = out_pitch[i];
+    segs.s[i].heads = heads[i], segs.s[i].rotate = rotate[i];
+    segs.total_heads += heads[i];
+  }
+  const size_t work = (size_t)tokens * segs.total_heads * (head_dim / 8);
+  qkv_rope_kernel<<<blocks_for(work), 256, 0, st>>>(segs, cos_t, sin_t, pos, tokens, head_dim, rot_dim, seq, mode,
+                                                    backward ? -1.f : 1.f);
   return (int)cudaGetLastError();
 }
 extern "C" int sb_bias_dropout_add(const void* x, const void* bias, const void* residual, void* out, long long n,

@@ -184,6 +184,30 @@ class ParallelSelfAttention(torch.nn.Module):
     def _sp(self) -> bool:
         return self.topology is not None and self.topology.config.sequence_parallel
 
+    def _project_qkv_rope(self, x: torch.Tensor, position_ids: Optional[torch.Tensor]):
+        """Fast path for the common layout (separate bias-free q/k/v projections adjacent in the arena, rotary, no
+        LoRA / QK-norm): ONE GEMM for q|k|v, then ONE kernel that splits the result and rotates q and k (and one kernel
+        back).  Returns None when it does not apply."""
+        if (self.qkv_in_one or self.rotary_embedding is None or self.key_query_norm or self.kv_replicas > 1
+                or (self.lora_config is not None and not self.lora_merged_state)):
+            return None
+        if any(m.get_bias() is not None for m in (self.query, self.key, self.value)):
+            return None
+        rot = self.rotary_embedding
+        nh, nkv, d = self.num_attention_heads_per_partition, self.num_kv_heads_per_partition, self.head_dim
+        weights = (self.query.weight, self.key.weight, self.value.weight)
+        if not OF.qkv_rope_fusable(x, d, rot.dimensions) or OF.fused_view(tuple(w.data for w in weights)) is None:
+            return None
+        comm = get_tp_comm(self.topology) if x.is_cuda else None
+        if comm is None and not self._sp():
+            x = copy_to_tensor_model_parallel_region(x, self.topology)
+        y = OF.multi_linear_fused(x, weights, comm=comm)
+        if y is None:
+            return None
+        s = x.shape[1]
+        pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
+        return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s, rot.mode, rot.dimensions)
+
     def _project_qkv(self, x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
         """x: [b, s, h] -> q [T, nh_local, d], k/v [T, nkv_local, d]."""
         b, s, _ = x.shape
@@ -213,20 +237,24 @@ class ParallelSelfAttention(torch.nn.Module):
         b, s, _ = x.shape
         T = b * s
         nh, d = self.num_attention_heads_per_partition, self.head_dim
-        q, k, v = self._project_qkv(x)
+        fused = self._project_qkv_rope(x, position_ids)
+        if fused is not None:
+            q, k, v = fused
+        else:
+            q, k, v = self._project_qkv(x)
 
-        if self.lora_config is not None and not self.lora_merged_state:
-            q, k, v = self._apply_lora(x, q, k, v)
+            if self.lora_config is not None and not self.lora_merged_state:
+                q, k, v = self._apply_lora(x, q, k, v)
 
-        if self.key_query_norm:
-            # every TP rank holds a replica of the per-head norm weights; norm over the local heads is identical math
-            q = self.norm_query(q, gather=False)
-            k = self.norm_key(k, gather=False)
+            if self.key_query_norm:
+                # every TP rank holds a replica of the per-head norm weights; norm over the local heads is identical math
+                q = self.norm_query(q, gather=False)
+                k = self.norm_key(k, gather=False)
 
-        if self.rotary_embedding is not None:
-            pos = None if position_ids is None else position_ids.reshape(-1)
-            q = self.rotary_embedding.apply_packed(q, pos, s)
-            k = self.rotary_embedding.apply_packed(k, pos, s)
+            if self.rotary_embedding is not None:
+                pos = None if position_ids is None else position_ids.reshape(-1)
+                q = self.rotary_embedding.apply_packed(q, pos, s)
+                k = self.rotary_embedding.apply_packed(k, pos, s)
 
         if cumulative_seq_lengths is None:
             cumulative_seq_lengths = torch.arange(0, T + 1, s, device=x.device, dtype=torch.int32)

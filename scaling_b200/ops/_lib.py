@@ -35,6 +35,7 @@ _SIGS = {
     "sb_act_fwd": [P, P, c_longlong, c_int, P],
     "sb_act_bwd": [P, P, P, c_longlong, c_int, P],
     "sb_rope": [P, P, P, P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, c_int, P],
+    "sb_qkv_rope": [P, P, P, P, P, P, c_int, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_bias_dropout_add": [P, P, P, P, c_longlong, c_int, c_float, c_ulonglong, c_ulonglong, P],
     "sb_dropout_bwd": [P, P, c_longlong, c_float, c_ulonglong, c_ulonglong, P],
     "sb_embedding_fwd": [P, P, P, c_int, c_int, c_longlong, c_longlong, P],

@@ -227,6 +227,18 @@ def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
         return None
 
 
+def multi_linear_fused(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None) -> Optional[torch.Tensor]:
+    """x·[W_0; W_1; …]ᵀ as one [..., ΣN_i] tensor when the weights are adjacent in the arena (see multi_linear), else None."""
+    if native_enabled(x) and x.dtype == torch.bfloat16 and all(_aligned(*w.shape) for w in weights) and x.numel() > 0:
+        fw = fused_view(tuple(w.data for w in weights))
+        if fw is not None:
+            mains = [getattr(w, "main_grad", None) for w in weights]
+            fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
+            if fmg is not None or all(m is None for m in mains):
+                return _MultiLinearFn.apply(x, fw, fmg, comm, *weights)
+    return None
+
+
 def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None) -> Tuple[torch.Tensor, ...]:
     """(x·W_0ᵀ, x·W_1ᵀ, …) — one GEMM when the weights are adjacent in the arena, separate linears otherwise.
     ``comm``: sum dX over the TP group inside the dgrad GEMM (column-parallel projections of a replicated input)."""
@@ -400,6 +412,56 @@ def rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[to
          rot_dim: int) -> torch.Tensor:
     """x: [tokens, heads, head_dim] bf16; cos/sin fp32 [max_pos, rot_dim/2]; pos int32 [tokens] or None."""
     return _RopeFn.apply(x, cos, sin, pos, seq, mode, rot_dim)
+
+
+class _QKVRopeFn(torch.autograd.Function):
+    """(q, k, v) = split(y) with rotary applied to q and k, as ONE kernel each way.
+
+    Forward reads the fused q|k|v GEMM output once and writes one contiguous [T, nh + 2·nkv, d] buffer (q, k, v are
+    views of it).  Backward reads dq, dk, dv once and writes the fused dY [T, (nh + 2·nkv)·d] that the dgrad / wgrad
+    GEMMs of the projections consume — replacing two strided clones + two rotary launches forward and two clones, two
+    rotary launches and a cat backward (reference: rotary after separate projections, attention.py:560-600)."""
+
+    @staticmethod
+    def forward(ctx, y, cos, sin, pos, seq, mode, rot_dim, nh, nkv, d):
+        T = y.shape[0]
+        ctx.save_for_backward(cos, sin, pos)
+        ctx.args = (seq, mode, rot_dim, nh, nkv, d, y.shape)
+        y2 = y.reshape(T, -1)
+        out = torch.empty((T, nh + 2 * nkv, d), dtype=y.dtype, device=y.device)
+        ins = _qkv_views(y2, nh, nkv, d)
+        outs = (out[:, :nh], out[:, nh:nh + nkv], out[:, nh + nkv:])
+        K.qkv_rope(ins, outs, (nh, nkv, nkv), (True, True, False), cos, sin, pos, seq, mode, rot_dim)
+        return outs
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        cos, sin, pos = ctx.saved_tensors
+        seq, mode, rot_dim, nh, nkv, d, shape = ctx.args
+        T = dq.shape[0]
+        dy = torch.empty((T, (nh + 2 * nkv) * d), dtype=dq.dtype, device=dq.device)
+        ins = tuple(g if (g.stride(2) == 1 and g.stride(1) == d) else g.contiguous() for g in (dq, dk, dv))
+        K.qkv_rope(ins, _qkv_views(dy, nh, nkv, d), (nh, nkv, nkv), (True, True, False), cos, sin, pos, seq, mode,
+                   rot_dim, backward=True)
+        return dy.view(shape), None, None, None, None, None, None, None, None, None
+
+
+def _qkv_views(y2: torch.Tensor, nh: int, nkv: int, d: int):
+    T = y2.shape[0]
+    q = y2[:, :nh * d].unflatten(1, (nh, d))
+    k = y2[:, nh * d:(nh + nkv) * d].unflatten(1, (nkv, d))
+    v = y2[:, (nh + nkv) * d:].unflatten(1, (nkv, d))
+    return q, k, v
+
+
+def qkv_rope_split(y: torch.Tensor, nh: int, nkv: int, d: int, cos: torch.Tensor, sin: torch.Tensor,
+                   pos: Optional[torch.Tensor], seq: int, mode: int, rot_dim: int):
+    """y: [..., (nh + 2·nkv)·d] fused projection output → (q [T, nh, d], k [T, nkv, d], v [T, nkv, d]), q and k rotated."""
+    return _QKVRopeFn.apply(y.reshape(-1, y.shape[-1]), cos, sin, pos, seq, mode, rot_dim, nh, nkv, d)
+
+
+def qkv_rope_fusable(x: torch.Tensor, d: int, rot_dim: int) -> bool:
+    return native_enabled(x) and x.dtype == torch.bfloat16 and d % 8 == 0 and rot_dim % 16 == 0 and 0 < rot_dim <= d
 
 
 # ------------------------------------------------------------------------------------------------ dropout + residual

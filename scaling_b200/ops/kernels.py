@@ -242,6 +242,26 @@ def rope_(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[t
     return x
 
 
+def qkv_rope(ins, outs, heads, rotate, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[torch.Tensor], seq: int,
+             mode: int, rot_dim: int, backward: bool = False) -> None:
+    """One pass over up to three [tokens, heads_i, d] segments (q, k, v): copy ``ins[i]`` to ``outs[i]`` (either may be
+    a strided slice of a fused buffer: unit stride inside a token, any token pitch), rotating the segments flagged in
+    ``rotate`` (inverse rotation when ``backward``)."""
+    import ctypes
+
+    n = len(ins)
+    tokens, _, d = ins[0].shape
+    for t in list(ins) + list(outs):
+        assert t.dtype == torch.bfloat16 and t.dim() == 3 and t.shape[0] == tokens and t.shape[2] == d
+        assert t.stride(2) == 1 and t.stride(1) == d
+    if pos is not None:
+        assert pos.dtype == torch.int32 and pos.is_contiguous()
+    U, L, I = ctypes.c_ulonglong * n, ctypes.c_longlong * n, ctypes.c_int * n
+    call("sb_qkv_rope", U(*[t.data_ptr() for t in ins]), U(*[t.data_ptr() for t in outs]), L(*[t.stride(0) for t in ins]),
+         L(*[t.stride(0) for t in outs]), I(*[int(h) for h in heads]), I(*[int(bool(r)) for r in rotate]), n, ptr(cos),
+         ptr(sin), ptr(pos), tokens, d, rot_dim, seq, mode, int(backward))
+
+
 def bias_dropout_add(x: torch.Tensor, bias: Optional[torch.Tensor], residual: Optional[torch.Tensor], p: float,
                      seed: int, offset: int) -> torch.Tensor:
     assert x.is_contiguous() and x.dtype == torch.bfloat16

@@ -199,6 +199,44 @@ def test_rope(K, mode):
     assert torch.equal(y, y2)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("rot_dim,d", [(128, 128), (64, 128), (32, 64)])
+def test_qkv_rope_split(K, mode, rot_dim, d):
+    """Fused split + rotary against the plain rotation formulas, forward and backward, with explicit position ids."""
+    from scaling_b200.ops import functional as OF
+
+    torch.manual_seed(4)
+    T, nh, nkv, seq = 96, 4, 2, 32
+    y = torch.randn(T, (nh + 2 * nkv) * d, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    pos = (torch.arange(T, device="cuda") % seq).flip(0).to(torch.int32).contiguous()
+    half = rot_dim // 2
+    inv = 1.0 / (10000 ** (torch.arange(0, half, device="cuda").float() / half))
+    ang = torch.arange(seq, device="cuda").float()[:, None] * inv[None]
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+
+    def ref_rot(x):  # x: [T, h, d] fp32
+        c, s_ = cos[pos.long()][:, None], sin[pos.long()][:, None]
+        r, rest = x[..., :rot_dim], x[..., rot_dim:]
+        if mode == 0:
+            a, b = r[..., 0::2], r[..., 1::2]
+            out = torch.stack((a * c - b * s_, a * s_ + b * c), dim=-1).flatten(-2)
+        else:
+            a, b = r[..., :half], r[..., half:]
+            out = torch.cat((a * c - b * s_, a * s_ + b * c), dim=-1)
+        return torch.cat((out, rest), dim=-1)
+
+    q, k, v = OF.qkv_rope_split(y, nh, nkv, d, cos, sin, pos, seq, mode, rot_dim)
+    yf = y.detach().float().requires_grad_(True)
+    qr = ref_rot(yf[:, :nh * d].view(T, nh, d))
+    kr = ref_rot(yf[:, nh * d:(nh + nkv) * d].view(T, nkv, d))
+    vr = yf[:, (nh + nkv) * d:].view(T, nkv, d)
+    assert _rel_err(q, qr) < 1e-2 and _rel_err(k, kr) < 1e-2 and torch.equal(v.float(), vr.detach())
+    gq, gk, gv = torch.randn_like(q), torch.randn_like(k), torch.randn_like(v)
+    torch.autograd.backward((q, k, v), (gq, gk, gv))
+    torch.autograd.backward((qr, kr, vr), (gq.float(), gk.float(), gv.float()))
+    assert _rel_err(y.grad, yf.grad) < 1e-2
+
+
 def test_bias_dropout_add(K):
     torch.manual_seed(6)
     x = torch.randn(512, 1024, device="cuda", dtype=torch.bfloat16)
