@@ -176,3 +176,30 @@ def test_non_distributed_mode_and_buffers_in_checkpoint(tmp_path):
     for (_, a), (_, b) in zip(model.local_layers(), fresh.local_layers()):
         for (n1, t1), (n2, t2) in zip(a.state_dict().items(), b.state_dict().items()):
             assert n1 == n2 and torch.equal(t1, t2), n1
+
+
+def test_profiler_output_feeds_the_schedule_simulator(tmp_path):
+    """Instruction profiler → profile.json (rank 0 gathers every rank's observations) → SimulationEngine replay."""
+    import json
+
+    from scaling_b200.core.nn import PipelineScheduleTrain, SimulationEngine
+
+    out = tmp_path / "profile.json"
+    cfg = {"topology": {"model_parallel_size": 1, "pipe_parallel_size": 2, "data_parallel_size": 1, "micro_batch_size": 2,
+                        "gradient_accumulation_steps": 4},
+           "trainer": {"train_iterations": 6, "assert_checkpoint_loaded": False, "seed": 1, "dataloader_pin_memory": False},
+           "profiler": {"profile_steps": 3, "profile_start_at_step": 2, "profiler_output": str(out)}}
+    dist_launcher(run_minimal, 2, config_dict=cfg)
+    data = json.loads(out.read_text())
+    assert data["pipe_parallel_size"] == 2 and data["gradient_accumulation_steps"] == 4
+    obs = data["observations"]
+    assert {o["pipe_parallel_rank"] for o in obs} == {0, 1}
+    names = {o["timer_name"] for o in obs}
+    assert {"ForwardPass", "BackwardPass", "SendActivation", "RecvActivation", "SendGrad", "RecvGrad", "OptimizerStep"} <= names
+    assert {o["step"] for o in obs} == {2, 3, 4} and all(o["duration"] >= 0 for o in obs)
+    sim = SimulationEngine.from_profile(PipelineScheduleTrain, out)
+    sim.simulate()
+    summary = sim.summarize()
+    assert summary["duration"] > 0 and len(summary["stages"]) == 2 and 0 <= summary["idle_percent"] < 100
+    assert sim.visualize() is not None
+    assert PipelineScheduleTrain.visualize_profile(out) is not None
