@@ -126,7 +126,14 @@ def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_raw_device = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def stream() -> int:
+    """Raw handle of the current stream of the current device (the C-level query skips building a Stream object)."""
+    if _raw_stream is not None and _raw_device is not None:
+        return _raw_stream(_raw_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -134,13 +141,13 @@ def call(name: str, *args, launches: int = 1) -> None:
     """Invoke a kernel entry point on the current stream and raise on a non-zero status."""
     global _launches
     lib = load(required=True)
-    dev = torch.cuda.current_device()
+    dev = _raw_device() if _raw_device is not None else torch.cuda.current_device()
     if getattr(_tls, "device", -1) != dev:  # e.g. an autograd worker thread making its first native call
         rc = lib.sb_bind_device(dev)
         if rc != 0:
             raise RuntimeError(f"sb_bind_device({dev}) failed with CUDA error {rc}")
         _tls.device = dev
-    rc = getattr(lib, name)(*args, stream())
+    rc = getattr(lib, name)(*args, _raw_stream(dev) if _raw_stream is not None else stream())
     if rc != 0:
         raise RuntimeError(f"{name} failed with status {rc}")
     _launches += launches

@@ -52,6 +52,7 @@ class TPComm:
         self.slot_bytes = 0
         self.flag_slot = 0
         self.calls = 0
+        self._need: Dict[tuple, int] = {}
         self._buf: Optional[torch.Tensor] = None
         self._hdl: Any = None
         self._data_ptrs = [None, None]
@@ -90,7 +91,9 @@ class TPComm:
     def reserve(self, m: int, n: int) -> None:
         """Make sure an [m, n] fused all-reduce fits.  Collective when it has to grow (all ranks ask for the same
         shapes in the same order, so they grow together)."""
-        need = int(_lib.host_lib().sb_gemm2_allreduce_slot_bytes(m, n))
+        need = self._need.get((m, n))
+        if need is None:
+            need = self._need[(m, n)] = int(_lib.host_lib().sb_gemm2_allreduce_slot_bytes(m, n))
         if need > self.slot_bytes:
             self._allocate(need)
 
