@@ -65,6 +65,10 @@ struct Params {
   // kAllReduce only
   int tp_rank, tp_size;
   uint32_t epoch;
+  // reduce-scatter mode (rs_seq > 0): rows are [batch, sequence]; rank r owns sequence positions
+  // [r·rs_seq_per_rank, (r+1)·rs_seq_per_rank) of every batch item (Megatron sequence parallelism).  A 256-row tile lies
+  // inside one rank's range; it is pushed to and reduced by that owner only, and D is the owner's compact [b·s/tp, N].
+  int rs_seq, rs_seq_per_rank;
   int debug;                      // timing experiments only (SB_AR_DEBUG): 1 no remote data, 2 wait own flags only, 4 no reduce
   uint32_t flag_slot;             // u32 flags per sender slot
   unsigned long long slot_bytes;  // bytes per sender slot
@@ -203,6 +207,13 @@ SB_DEVICE void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
   int r = t - g * per_group;
   tm = first_m + r % gsize;
   tn = r / gsize;
+}
+
+// Reduce-scatter mode: which rank owns the tile whose first row is `row0`, and where that row lands in the owner's D.
+SB_DEVICE int rs_owner(const Params& p, int row0) { return (row0 % p.rs_seq) / p.rs_seq_per_rank; }
+SB_DEVICE int rs_out_row(const Params& p, int row) {
+  const int b = row / p.rs_seq, s = row % p.rs_seq;
+  return b * p.rs_seq_per_rank + s % p.rs_seq_per_rank;
 }
 
 // Work unit u of the persistent schedule -> (tile, k-block range, part index or -1 when the tile is not split).
@@ -384,8 +395,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         done += 4;
         while (ld_acquire_cta_smem(&bars->pushed) < done) __nanosleep(40);
         fence_acq_rel_sys();  // the four warps' bulk copies (completed, observed through `pushed`) before the flags
-        for (int r = 0; r < p.tp_size; ++r)
-          st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
+        if (p.rs_seq > 0) {
+          int tm_, tn_;
+          tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
+          st_relaxed_sys(p.ar_flags[rs_owner(p, tm_ * BM)] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
+        } else {
+          for (int r = 0; r < p.tp_size; ++r)
+            st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
+        }
       }
     }
   } else if (kEpi == kAllReduce && warp >= 8) {
@@ -399,6 +416,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
       const uint32_t ct = (uint32_t)t * 2 + rank;
       if (p.debug & 4) continue;
+      if (p.rs_seq > 0 && rs_owner(p, tm * BM) != p.tp_rank) continue;  // another rank reduces this tile
       if (lane == 0) {
         for (int s = 0; s < p.tp_size; ++s)
           if (!(p.debug & 2) || s == p.tp_rank) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
@@ -428,7 +446,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           const int row = row0 + r_in;
           const int col = n0 + c4 * 64 + j * 8;
           if (row >= p.M || col >= p.N) continue;
-          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd + col;
+          const int drow = p.rs_seq > 0 ? rs_out_row(p, row) : row;
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)drow * p.ldd + col;
           if (col + 8 <= p.N) {
             if (bias) {
               const uint4 bv = *reinterpret_cast<const uint4*>(bias + col);
@@ -456,6 +475,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
       const size_t slab_off = (size_t)p.tp_rank * p.slot_bytes + ((size_t)ct * 4 + ew) * kSlabBytes;
+      int rs_tile_owner = 0;
+      if (p.rs_seq > 0) {
+        int tm_, tn_;
+        tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
+        rs_tile_owner = rs_owner(p, tm_ * BM);
+      }
 #pragma unroll 1
       for (int c4 = 0; c4 < 4; ++c4) {
         uint8_t* buf = staging + (c4 & 1) * kChunkBytes;
@@ -484,9 +509,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          for (int r = 0; r < p.tp_size; ++r)
-            if (!(p.debug & 1) || r == p.tp_rank)
-              bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
+          if (p.rs_seq > 0) {
+            bulk_store_s2g(p.ar_data[rs_tile_owner] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
+          } else {
+            for (int r = 0; r < p.tp_size; ++r)
+              if (!(p.debug & 1) || r == p.tp_rank)
+                bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
+          }
           bulk_commit();
         }
       }
@@ -856,11 +885,11 @@ extern "C" int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void*
 // into this process; `epoch` must be unique per call on a workspace parity and equal on all ranks.  Replaces the
 // reference's GEMM followed by torch.distributed.all_reduce (core/nn/linear/row_parallel_linear.py:150-160, and the
 // backward all-reduce of core/nn/linear/utils.py copy_to_tensor_model_parallel_region).
-extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
-                                       int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
-                                       const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
-                                       unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas,
-                                       cudaStream_t stream) {
+static int fused_collective_impl(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
+                                 int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
+                                 const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                                 unsigned long long slot_bytes, unsigned int flag_slot, int rs_seq, int max_ctas,
+                                 cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if (tp_size < 2 || tp_size > kMaxTP || tp_rank < 0 || tp_rank >= tp_size) return -20;
   CUtensorMap ta, tb;
@@ -889,6 +918,7 @@ extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, co
     }
     p.debug = dbg;
   }
+  p.rs_seq = rs_seq, p.rs_seq_per_rank = rs_seq > 0 ? rs_seq / tp_size : 0;
   p.tp_rank = tp_rank, p.tp_size = tp_size, p.epoch = epoch, p.flag_slot = flag_slot, p.slot_bytes = slot_bytes;
   for (int r = 0; r < tp_size; ++r) {
     p.ar_data[r] = reinterpret_cast<uint8_t*>(data_ptrs[r]);
@@ -897,6 +927,29 @@ extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, co
   if (a_layout == 0 && b_layout == 0) return launch<0, 0, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
   if (a_layout == 0 && b_layout == 1) return launch<0, 1, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
   return -10;
+}
+
+// Fused tensor-parallel GEMM + reduce-scatter along the sequence (Megatron sequence parallelism): rows of the product
+// are [batch, seq]; rank r receives the sum over ranks of its sequence slice, D = [batch · seq/tp, N] compact.  Same
+// workspace / epoch contract as sb_gemm2_allreduce_bf16; requires (seq / tp_size) % 256 == 0 and M % seq == 0.
+// Reference: F.linear then reduce_scatter (core/nn/linear/utils.py:279-300, attention.py:704-705, mlp.py:164-165).
+extern "C" int sb_gemm2_reduce_scatter_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K,
+                                            int lda, int ldb, int ldd, int a_layout, int b_layout,
+                                            const unsigned long long* data_ptrs, const unsigned long long* flag_ptrs,
+                                            int tp_rank, int tp_size, unsigned int epoch, unsigned long long slot_bytes,
+                                            unsigned int flag_slot, int seq, int max_ctas, cudaStream_t stream) {
+  if (seq <= 0 || M % seq || seq % tp_size || (seq / tp_size) % BM) return -22;
+  return fused_collective_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, a_layout, b_layout, data_ptrs, flag_ptrs, tp_rank,
+                               tp_size, epoch, slot_bytes, flag_slot, seq, max_ctas, stream);
+}
+
+extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
+                                       int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
+                                       const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                                       unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas,
+                                       cudaStream_t stream) {
+  return fused_collective_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, a_layout, b_layout, data_ptrs, flag_ptrs, tp_rank,
+                               tp_size, epoch, slot_bytes, flag_slot, 0, max_ctas, stream);
 }
 
 // Bytes of workspace one sender slot needs for an [M, N] fused all-reduce, and flags per slot.

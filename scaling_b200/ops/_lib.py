@@ -28,6 +28,8 @@ _SIGS = {
     "sb_gemm2_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_allreduce_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int,
                                 c_uint, c_ulonglong, c_uint, c_int, P],
+    "sb_gemm2_reduce_scatter_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int,
+                                     c_uint, c_ulonglong, c_uint, c_int, c_int, P],
     "sb_norm_fwd": [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, c_int, P],
     "sb_norm_bwd": [P, P, P, P, P, P, P, P, P, c_int, c_int, P, c_int, c_int, c_int, c_int, P],
     "sb_swiglu_fwd": [P, P, c_int, c_int, P],

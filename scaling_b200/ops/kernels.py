@@ -124,6 +124,36 @@ def gemm_allreduce(a: torch.Tensor, b: torch.Tensor, comm, *, b_mn: bool = False
     return out
 
 
+def reduce_scatter_supported(M: int, seq: int, tp: int) -> bool:
+    """Sequence slices must be whole 256-row tiles."""
+    return seq > 0 and M % seq == 0 and seq % tp == 0 and (seq // tp) % 256 == 0
+
+
+def gemm_reduce_scatter(a: torch.Tensor, b: torch.Tensor, comm, seq: int, *, b_mn: bool = False,
+                        bias: Optional[torch.Tensor] = None, max_ctas: int = 0) -> torch.Tensor:
+    """D[M/tp, N] = this rank's sequence slice of Σ_ranks A_r · B_rᵀ (+ bias) in ONE launch (rows of A are [batch, seq];
+    rank r keeps positions [r·seq/tp, (r+1)·seq/tp) of every batch item).  Partial tiles travel over NVLink to their
+    owner only — half the bytes of the fused all-reduce at tp = 2 — while later tiles are in the tensor cores."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    M, K = a.shape
+    N = b.shape[1] if b_mn else b.shape[0]
+    assert (b.shape[0] if b_mn else b.shape[1]) == K
+    assert reduce_scatter_supported(M, seq, comm.size), (M, seq, comm.size)
+    out = torch.empty((M // comm.size, N), dtype=torch.bfloat16, device=a.device)
+    lda, ldb, ldd = a.stride(0), b.stride(0), out.stride(0)
+    assert gemm_supported(M, N, K, lda, ldb, ldd)
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    comm.reserve(M, N)
+    epoch, data_ptrs, flag_ptrs = comm.next_call()
+    call(
+        "sb_gemm2_reduce_scatter_bf16", ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, 0, int(b_mn),
+        data_ptrs, flag_ptrs, comm.rank, comm.size, epoch, comm.slot_bytes, comm.flag_slot, seq, max_ctas,
+    )
+    return out
+
+
 def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """h = silu(x·W1ᵀ) ⊙ (x·W2ᵀ) with ``w_gate_up`` = [W1; W2] ([2F, K]); returns (h [M,F], pre [M,2F] or None)."""
     assert x.dtype == torch.bfloat16 and w_gate_up.dtype == torch.bfloat16

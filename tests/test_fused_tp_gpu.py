@@ -45,6 +45,52 @@ def _kernel_worker(rank: int, world_size: int, master_port: int):
     return worst
 
 
+def _rs_worker(rank: int, world_size: int, master_port: int):
+    import torch.distributed as dist
+
+    from scaling_b200.ops import kernels as K
+    from scaling_b200.parallel.symm import TPComm
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{master_port}", rank=rank, world_size=world_size,
+                            device_id=torch.device("cuda", rank))
+    comm = TPComm(dist.group.WORLD, torch.device("cuda", rank))
+    worst = 0.0
+    for (batch, seq, N, Kd, b_mn, has_bias) in [(1, 512 * world_size, 256, 128, False, False),
+                                                (2, 256 * world_size, 520, 192, False, True),
+                                                (3, 256 * world_size, 384, 320, True, False)]:
+        M = batch * seq
+        g = torch.Generator(device="cuda").manual_seed(17 + rank)
+        a = torch.randn(M, Kd, device="cuda", generator=g).bfloat16()
+        b = (torch.randn((Kd, N) if b_mn else (N, Kd), device="cuda", generator=g) * 0.1).bfloat16()
+        bias = torch.randn(N, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3)).bfloat16() if has_bias else None
+        full = a.float() @ (b.float() if b_mn else b.float().t())
+        dist.all_reduce(full)
+        if bias is not None:
+            full = full + bias.float()
+        per = seq // world_size
+        want = full.view(batch, seq, N)[:, rank * per:(rank + 1) * per].reshape(batch * per, N)
+        for _ in range(3):
+            out = K.gemm_reduce_scatter(a, b, comm, seq, b_mn=b_mn, bias=bias)
+        # interleave with the all-reduce flavour on the same workspace: epochs / parity are shared
+        ar = K.gemm_allreduce(a, b, comm, b_mn=b_mn, bias=bias)
+        torch.cuda.synchronize()
+        assert out.shape == want.shape
+        err = ((out.float() - want).abs().max() / want.abs().max()).item()
+        err_ar = ((ar.float() - full).abs().max() / full.abs().max()).item()
+        assert err < 2e-2 and err_ar < 2e-2, (batch, seq, N, Kd, err, err_ar)
+        worst = max(worst, err)
+    return worst
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_gemm_reduce_scatter_kernel(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    res = dist_launcher(_rs_worker, world_size=world, timeout=300)
+    assert len(res) == world and all(v < 2e-2 for v in res.values())
+
+
 def _stress_worker(rank: int, world_size: int, master_port: int, iters: int):
     """Signal/wait protocol under skew: ranks are delayed by random amounts before (and between) launches, shapes and
     layouts change from call to call, and results are checked against NCCL every time.  A lost flag, a stale-parity
