@@ -44,6 +44,27 @@ int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, const void* b
                             const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
                             unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas, cudaStream_t st);
 long long sb_gemm2_allreduce_slot_bytes(int M, int N);
+/* Same launch, reduce-scatter along the sequence (Megatron sequence parallelism): rows of the product are [batch, seq],
+ * rank r receives its slice seq/tp of every batch item, D = [M / tp_size, N]; needs (seq / tp_size) % 256 == 0.
+ * Reference counterpart: F.linear then reduce_scatter (core/nn/linear/utils.py:279-300). */
+int sb_gemm2_reduce_scatter_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda,
+                                 int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
+                                 const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                                 unsigned long long slot_bytes, unsigned int flag_slot, int seq, int max_ctas,
+                                 cudaStream_t st);
+/* Fused ZeRO-1 step over data-parallel peer memory (csrc/optim.cu): reduce-scatter as peer loads, all-gather as peer
+ * stores inside AdamW.  Reference counterpart: all-reduce + slice, AdamW, all_gather (parameter_group.py:346-481). */
+int sb_zero_reduce(const unsigned long long* peer_grads, int n_peers, void* own, long long n, int grad_dtype,
+                   cudaStream_t st);
+int sb_adamw_zero(float* p32, float* m, float* v, void* g, const unsigned long long* peer_outs, int n_peers, long long n,
+                  int grad_dtype, int out_dtype, float lr, float beta1, float beta2, float eps, float weight_decay,
+                  int step, float inv_loss_scale, float clip, const float* norm_sq, const int* skip, int zero_grad,
+                  cudaStream_t st);
+/* Fused q|k|v split + rotary over up to three head segments (csrc/elementwise.cu). */
+int sb_qkv_rope(const unsigned long long* ins, const unsigned long long* outs, const long long* in_pitch,
+                const long long* out_pitch, const int* heads, const int* rotate, int n_seg, const float* cos_t,
+                const float* sin_t, const int* pos, int tokens, int head_dim, int rot_dim, int seq, int mode,
+                int backward, cudaStream_t st);
 
 /* Flash attention for packed (varlen) sequences, head_dim 128, bf16, GQA; tcgen05 + TMEM + TMA.
  * q/out: [T, heads, 128] (row pitch q_pitch elements), k/v: [T, kv_heads, 128]; seg_start/seg_end: per token, the

@@ -302,7 +302,10 @@ class ParallelSelfAttention(torch.nn.Module):
         ctx = ctx.reshape(b, s, nh * d)
 
         if self._sp():
-            out = all_reduce_scatter_to_sequence_parallel(self.dense(ctx), self.topology)
+            out = OF.linear_reduce_scatter(ctx, self.dense.weight, get_tp_comm(self.topology, sequence_parallel=True)) \
+                if ctx.is_cuda else None
+            if out is None:
+                out = all_reduce_scatter_to_sequence_parallel(self.dense(ctx), self.topology)
             bias = self.dense.get_bias()
             if bias is not None:
                 out = out + bias

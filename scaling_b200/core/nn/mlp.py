@@ -35,7 +35,11 @@ def _row_parallel_out(layer: RowParallelLinear, h: torch.Tensor, topology: Optio
     GEMM launch when the TP group has a peer-memory communicator) and the bias added once."""
     if not _sp(topology):
         return layer(h, reduce=True)
-    y = all_reduce_scatter_to_sequence_parallel(layer(h), topology)
+    y = None
+    if layer.parallel_input and h.is_cuda:  # fused GEMM + reduce-scatter over NVLink peer memory
+        y = OF.linear_reduce_scatter(h, layer.weight, get_tp_comm(topology, sequence_parallel=True))
+    if y is None:
+        y = all_reduce_scatter_to_sequence_parallel(layer(h), topology)
     b = layer.get_bias()
     return y if b is None else y + b
 

@@ -141,6 +141,44 @@ class _LinearFn(torch.autograd.Function):
         return dx, dw, db, None, None, None
 
 
+class _LinearReduceScatterFn(torch.autograd.Function):
+    """Row-parallel projection under sequence parallelism: y[b, s/tp, N] = reduce-scatter_seq(x·Wᵀ) as ONE launch
+    (reference: F.linear, then reduce_scatter along the sequence, attention.py:704-705 / mlp.py:164-165).  Backward
+    all-gathers dY along the sequence (NCCL) and runs the ordinary dgrad / wgrad GEMMs."""
+
+    @staticmethod
+    def forward(ctx, x, weight, comm):
+        b, s, k = x.shape
+        x2 = x.reshape(b * s, k)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y = K.gemm_reduce_scatter(x2, weight, comm, s)
+        ctx.save_for_backward(x2, weight)
+        ctx.comm, ctx.x_shape = comm, x.shape
+        return y.view(b, s // comm.size, weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from ..core.nn.tp_ops import _all_gather_seq
+
+        x2, weight = ctx.saved_tensors
+        dy_full = _all_gather_seq(dy.contiguous(), ctx.comm.size, ctx.comm.group)
+        dy2 = dy_full.reshape(-1, dy_full.shape[-1])
+        dx = _gemm_nn(dy2, weight).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw = _accumulate_wgrad(dy2, x2, weight) if ctx.needs_input_grad[1] else None
+        return dx, dw, None
+
+
+def linear_reduce_scatter(x: torch.Tensor, weight: torch.Tensor, comm) -> Optional[torch.Tensor]:
+    """Fused row-parallel GEMM + sequence reduce-scatter, or None when the shapes do not fit the fused kernel (the
+    caller then runs GEMM + NCCL reduce-scatter)."""
+    if (comm is None or x.dim() != 3 or not native_enabled(x) or x.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16
+            or not _aligned(*weight.shape) or not K.reduce_scatter_supported(x.shape[0] * x.shape[1], x.shape[1], comm.size)
+            or weight.shape[0] < 128):
+        return None
+    return _LinearReduceScatterFn.apply(x, weight, comm)
+
+
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, *, comm=None,
            reduce_output: bool = False, reduce_input_grad: bool = False) -> torch.Tensor:
     """y = x·Wᵀ (+ b) — replaces F.linear in Column/RowParallelLinear (reference column_parallel_linear.py:151).

@@ -156,13 +156,16 @@ class SymmetricArena:
         return arr(*[p + element_offset * self.itemsize for p in self.peer_ptrs])
 
 
-def get_tp_comm(topology: Any) -> Optional[TPComm]:
+def get_tp_comm(topology: Any, sequence_parallel: bool = False) -> Optional[TPComm]:
     """The fused-collective communicator of ``topology``'s TP group, or None when the fused path does not apply
-    (single TP rank, sequence parallelism, CPU / gloo, disabled by SCALING_B200_FUSED_TP=0)."""
+    (single TP rank, CPU / gloo, disabled by SCALING_B200_FUSED_TP=0).  Plain tensor parallelism uses it for the fused
+    GEMM + all-reduce; ``sequence_parallel=True`` returns it for sequence-parallel jobs (fused GEMM + reduce-scatter)."""
     if topology is None or not _ENABLED:
         return None
     c = topology.config
-    if c.model_parallel_size == 1 or c.sequence_parallel or not topology.is_distributed_initialized:
+    if c.model_parallel_size == 1 or not topology.is_distributed_initialized:
+        return None
+    if bool(c.sequence_parallel) != bool(sequence_parallel):  # callers ask for the communicator of THEIR mode
         return None
     if topology.backend != "nccl" or topology.device.type != "cuda" or not _lib.available():
         return None

@@ -158,6 +158,8 @@ def _train_worker(rank: int, world_size: int, master_port: int, config_dict, fus
                           local_slot=rank, payload=config_dict)
     metrics = main(launch, return_metrics=True)
     assert _lib.launch_count() > n0
+    fused_calls = sum(c.calls for c in symm._COMMS.values())
+    assert (fused_calls > 0) == fused, f"fused collective kernels ran {fused_calls} times with fused={fused}"
     return [m["training/loss"] for m in (metrics or [])]
 
 
@@ -232,3 +234,18 @@ def test_dp2_fused_zero_matches_nccl(tmp_path):
     assert len(fused) == 6
     assert fused == plain, (fused, plain)
     assert fused[-1][0] < fused[0][0]
+
+
+def test_sequence_parallel_fused_reduce_scatter_matches_nccl(tmp_path):
+    """Sequence-parallel TP=2 training with the row-parallel reduce-scatters inside the GEMM launch against the same
+    run on NCCL reduce-scatters."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=1024, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
+         "sequence_length": 512, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"}}
+    cfg = tiny_config(prefix, mp=2, iters=5, gas=2, arch=a, topology={"sequence_parallel": True})
+    fused = dist_launcher(_train_worker, world_size=2, timeout=400, config_dict=cfg, fused=True)[0]
+    plain = dist_launcher(_train_worker, world_size=2, timeout=400, config_dict=cfg, fused=False)[0]
+    assert len(fused) == 5 and all(x == x for x in fused)
+    for x, y in zip(fused, plain):
+        assert abs(x - y) / abs(y) < 2e-2, (fused, plain)
