@@ -10,6 +10,7 @@ from typing import Any, Dict, List, Tuple, Union
 import torch
 
 from scaling_b200.core import (
+    BaseContext,
     BaseLayer,
     BaseLayerIO,
     ColumnParallelLinear,
@@ -22,8 +23,14 @@ from scaling_b200.core import (
     Topology,
 )
 
-from .context import MLPContext
+from .config import MLPConfig
 from .data import MNISTDatasetBatch
+
+
+class MLPContext(BaseContext[MLPConfig]):
+    """Run state of the example (iteration / sample counters, RNG, topology) typed with the example's config."""
+
+    config: MLPConfig
 
 
 class MLPLayerIO(BaseLayerIO):
@@ -113,7 +120,7 @@ def init_optimizer(context: MLPContext, model: ParallelModule) -> Optimizer:
     lr = context.config.learning_rate_scheduler
     groups = [
         OptimizerParamGroup([x for x in named if not x[0].endswith("bias")],
-                            OptimizerParamGroupConfig(name="weight_decay_params", weight_decay=context.config.training.weight_decay,
+                            OptimizerParamGroupConfig(name="weight_decay_params", weight_decay=context.config.architecture.weight_decay,
                                                       learning_rate_scheduler=lr)),
         OptimizerParamGroup([x for x in named if x[0].endswith("bias")],
                             OptimizerParamGroupConfig(name="no_weight_decay_params", weight_decay=0.0, learning_rate_scheduler=lr)),

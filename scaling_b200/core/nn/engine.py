@@ -15,7 +15,7 @@ from __future__ import annotations
 import collections
 import time
 from enum import Enum
-from typing import Any, Callable, Dict, Generic, List, NamedTuple, Optional, Tuple, Union
+from typing import TYPE_CHECKING, Any, Callable, Dict, Generic, List, NamedTuple, Optional, Tuple, Union
 
 import torch
 import torch.distributed as dist
@@ -23,7 +23,6 @@ from torch.utils._pytree import tree_map
 
 from ..data.base import BaseDatasetBatch
 from ..logging import logger
-from ..optimizer import BaseOptimizer
 from ..profiler import Profiler, ProfilerConfig, SynchronizedTimer
 from ..topology import ActivationCheckpointingType, Topology
 from .act_ckpt import checkpoint
@@ -47,6 +46,10 @@ from .schedule import (
     PipelineScheduleInference,
     PipelineScheduleTrain,
 )
+
+
+if TYPE_CHECKING:  # only for annotations: core.optimizer imports core.nn
+    from ..optimizer import BaseOptimizer
 
 
 class BufferType(Enum):
@@ -245,7 +248,7 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
         return checkpoint(run_stage, self.topology, *first.input_to_tuple(x))
 
     # ---- steps --------------------------------------------------------------------------------------------
-    def train_step(self, dataloader: Optional[Any], optimizer: BaseOptimizer,
+    def train_step(self, dataloader: Optional[Any], optimizer: "BaseOptimizer",
                    sync_batch_to_model_parallel: Callable[[Topology, Optional[Any]], Any],
                    loss_function: Callable[..., Any], metrics_aggregation_fn: Optional[Callable] = None) -> TrainStepOutput:
         self.step_timer.start()
@@ -280,7 +283,7 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
         return EvaluationStepOutput(loss, metrics, self.step_timer.stop())
 
     def run_instructions(self, instructions: List[InstructionBase], dataloader: Optional[Any] = None,
-                         optimizer: Optional[BaseOptimizer] = None, sync_batch_to_model_parallel: Optional[Callable] = None,
+                         optimizer: Optional["BaseOptimizer"] = None, sync_batch_to_model_parallel: Optional[Callable] = None,
                          loss_function: Optional[Callable] = None) -> Buffers:
         """Interpret an arbitrary instruction list (inference-style use); returns the buffers."""
         self.pipe_buffer.reset()
