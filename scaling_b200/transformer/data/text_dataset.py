@@ -132,6 +132,9 @@ class TextDataset(BaseDataset[TextDatasetItem, TextDatasetBatchBeforeSync, TextD
     def __getitem__(self, index: int) -> TextDatasetItem:
         assert self.data_item_index is not None, "data item index not set"
         pieces = np.asarray(self.data_item_index[index]).reshape(-1, 3)
+        native = self._native_gather(pieces)
+        if native is not None:
+            return TextDatasetItem(token_ids=torch.from_numpy(native.astype(np.int64)))
         out = np.empty(self.sequence_length + 1, dtype=np.int64)
         w = 0
         for doc, start, end in pieces.tolist():
@@ -139,6 +142,35 @@ class TextDataset(BaseDataset[TextDatasetItem, TextDatasetBatchBeforeSync, TextD
             out[w:w + n] = self.memory_map[doc][start:end]
             w += n
         return TextDatasetItem(token_ids=torch.from_numpy(out))
+
+    def _native_gather(self, pieces: np.ndarray) -> Optional[np.ndarray]:
+        """The window's (document, start, end) pieces copied by the C++ ``sb_gather_window_i32`` straight out of the
+        memory-mapped int32 token file (the reference loops over the pieces in Python,
+        text_dataset.py:371-385).  None when the corpus is not an int32 memory map or the library is unavailable."""
+        state = getattr(self, "_gather_state", None)
+        if state is None:
+            state = False
+            if isinstance(self.memory_map, MemoryMapDataset) and not self.legacy_dataset:
+                try:
+                    import ctypes
+
+                    from ...ops._lib import host_lib
+
+                    tokens = self.memory_map.tokens()
+                    if tokens.dtype == np.int32:
+                        offsets = np.ascontiguousarray(self.memory_map.offsets(), dtype=np.int64)
+                        state = (host_lib().sb_gather_window_i32, ctypes, tokens, offsets)
+                except (RuntimeError, OSError, AttributeError):
+                    state = False
+            self._gather_state = state
+        if state is False:
+            return None
+        fn, ctypes, tokens, offsets = state
+        out = np.empty(self.sequence_length + 1, dtype=np.int32)
+        p64 = np.ascontiguousarray(pieces, dtype=np.int64)
+        n = fn(tokens.ctypes.data_as(ctypes.c_void_p), offsets.ctypes.data_as(ctypes.c_void_p),
+               p64.ctypes.data_as(ctypes.c_void_p), len(p64), out.ctypes.data_as(ctypes.c_void_p), len(out))
+        return out if n == len(out) else None
 
     def collate(self, batch: List[TextDatasetItem]) -> TextDatasetBatchBeforeSync:
         return TextDatasetBatchBeforeSync(token_ids=torch.stack([b.token_ids for b in batch]))

@@ -301,3 +301,22 @@ def test_inference_module_matches_training_module(tmp_path):
     model = TransformerInferenceModule.from_checkpoint(step_dir, devices=["cpu"])
     logits = model.logits(input_tokens=[5, 16, 49, 21, 64, 3, 10, 31])
     assert torch.allclose(logits.float(), trained.squeeze(0), atol=1e-5)
+
+
+def test_native_window_gather_matches_python_loop(tmp_path):
+    """int32 corpora take the C++ gather; it must return exactly what the Python piece loop returns."""
+    from scaling_b200.core import MemoryMapDatasetBuilder
+    from scaling_b200.transformer.data import TextDataset
+
+    rng = np.random.default_rng(3)
+    with MemoryMapDatasetBuilder(tmp_path / "c32", dtype=np.int32) as b:
+        for n in (7, 90, 3, 41, 64, 12, 55):
+            d = rng.integers(1, 1000, size=n)
+            d[-1] = 0
+            b.add(d)
+    ds = TextDataset(tmp_path / "c32", sequence_length=32, seed=5)
+    native = [ds[i].token_ids.clone() for i in range(len(ds))]
+    assert ds._gather_state is not False, "native gather was not used for an int32 memory map"
+    ds._gather_state = False  # force the Python loop
+    assert all(torch.equal(a, ds[i].token_ids) for i, a in enumerate(native))
+    assert native[0].dtype == torch.int64 and native[0].shape == (33,)
