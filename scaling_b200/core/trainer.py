@@ -165,6 +165,19 @@ class BaseTrainer(Generic[BaseContextGeneric, ParallelModuleGeneric]):
         self.context.consumed_samples_evaluation += self.context.topology.config.global_batch_size
         return out
 
+    def evaluate(self) -> EvaluationStepOutput:
+        """``eval_iterations`` evaluation steps (each one global batch) averaged into one result — the reference defines
+        the option but runs a single step regardless (SURVEY §9.2 #18)."""
+        outs = [self.eval_step() for _ in range(max(1, int(self.config.eval_iterations or 1)))]
+        if len(outs) == 1:
+            return outs[0]
+        n = float(len(outs))
+        metrics = None
+        if outs[0].metrics is not None:
+            metrics = {k: sum(o.metrics[k] for o in outs) / n for k in outs[0].metrics}
+        loss = None if outs[0].loss is None else sum(o.loss for o in outs) / n
+        return EvaluationStepOutput(loss, metrics, sum(o.step_duration for o in outs))
+
     def log_metrics(self, train_step_output: TrainStepOutput, eval_step_output: Optional[EvaluationStepOutput]) -> Dict[str, Any]:
         logger.info(f"completed step {self.context.iterations}")
         t = train_step_output
@@ -209,7 +222,7 @@ class BaseTrainer(Generic[BaseContextGeneric, ParallelModuleGeneric]):
                 self.save_checkpoint()
             ev = None
             if self.config.eval_interval is not None and self.context.iterations % self.config.eval_interval == 0:
-                ev = self.eval_step()
+                ev = self.evaluate()
             if self.context.topology.config.global_rank == 0:
                 m = self.log_metrics(out, ev)
                 if return_metrics:

@@ -93,7 +93,7 @@ def test_model_parallel_communicator():
     assert all(dist_launcher(_mp_comm_worker, 2).values())
 
 
-def _eval_worker(rank: int, world_size: int, master_port: int, pp: int):
+def _eval_worker(rank: int, world_size: int, master_port: int, pp: int, eval_iterations: int = 1):
     """Evaluation runs gradient_accumulation_steps micro batches through the inference schedule under no_grad and
     reports evaluation/* metrics every eval_interval steps; parameters are untouched by it."""
     import torch
@@ -112,7 +112,7 @@ def _eval_worker(rank: int, world_size: int, master_port: int, pp: int):
         "topology": {"model_parallel_size": 1, "pipe_parallel_size": pp, "data_parallel_size": 1, "micro_batch_size": 2,
                      "gradient_accumulation_steps": 2, "world_size": world_size, "global_rank": rank, "local_slot": rank},
         "trainer": {"train_iterations": 4, "assert_checkpoint_loaded": False, "eval_interval": 2, "seed": 1,
-                    "dataloader_pin_memory": False}})
+                    "dataloader_pin_memory": False, "eval_iterations": eval_iterations}})
     topo = Topology(cfg.topology)
     ctx = MinimalContext(config=cfg, topology=topo)
     ctx.initialize(master_addr="127.0.0.1", master_port=str(master_port), seed=1)
@@ -141,6 +141,12 @@ def test_evaluation_step(pp):
     assert [bool(k) for k in res["keys"]] == [False, True, False, True]
     assert "evaluation/loss" in res["keys"][1]
     assert res["consumed_eval"] == 3 * 4  # one explicit + two scheduled evaluations of global batch 4
+
+
+def test_eval_iterations_average_several_steps():
+    res = dist_launcher(_eval_worker, 1, pp=1, eval_iterations=3)[0]
+    assert res["consumed_eval"] == (1 + 2 * 3) * 4  # one explicit step + two evaluations of three steps each
+    assert "evaluation/loss" in res["keys"][1]
 
 
 def test_non_distributed_mode_and_buffers_in_checkpoint(tmp_path):
