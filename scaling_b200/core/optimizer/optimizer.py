@@ -231,7 +231,10 @@ class Optimizer(BaseOptimizer):
                     name = f"{m.parameter_name}-layer-{m.layer_index}"
                     debug[f"debug/{name}-norm"] = float(p.float().norm().item())
                     debug[f"debug/{name}-pct-zero"] = 1.0 - float((p.count_nonzero() / max(p.numel(), 1)).item())
-        return OptimizerStepOutput(global_grad_norm, None, learning_rates, overflow, ls.no_overflow_steps,
+        # norm after clipping (the reference declares the field and always returns None)
+        clipped = min(global_grad_norm, c.gradient_clipping) if c.gradient_clipping and c.gradient_clipping > 0 \
+            else global_grad_norm
+        return OptimizerStepOutput(global_grad_norm, clipped, learning_rates, overflow, ls.no_overflow_steps,
                                    ls.current_loss_scale, debug)
 
     def refresh_optimizer_after_model_change(self) -> None:
