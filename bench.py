@@ -243,6 +243,25 @@ def timed_steps(step_fn, warmup: int, steps: int, world: int, local: int):
     return float(ms.item()), clocks, last
 
 
+def mfu_block(args, tokens_per_s: float, n: int) -> dict:
+    """PaLM model-FLOP utilisation, `tokens/s * (6 N + 12 L h s) / (peak * n_gpus)` with N = unique parameters
+    (the reference's definition, src/scaling/transformer/utils/get_tflops.py:365-401, which itself divides by zero on
+    B200).  Reported against the vendor dense bf16 peak and against the driver-measured cuBLAS sustained rate."""
+    h, L, f, V, kvw = 4096, args.layers, 14336, 32000, 8 * 128
+    n_params = L * (2 * h * h + 2 * h * kvw + 3 * h * f + 2 * h) + 2 * V * h + h
+    flop_per_token = 6 * n_params + 12 * L * h * SEQ
+    achieved = tokens_per_s * flop_per_token / n
+    out = {"definition": "palm 6N+12Lhs, N=unique params", "params": n_params,
+           "tflops_per_gpu": achieved / 1e12, "vs_vendor_peak_2250": achieved / 2.25e15}
+    try:
+        peaks = json.load(open(REPO / "MEASURED_PEAKS.json"))
+        out["vs_measured_sustained"] = achieved / (float(peaks["bf16_tflops_sustained"]) * 1e12)
+        out["measured_sustained_tflops"] = float(peaks["bf16_tflops_sustained"])
+    except Exception:  # noqa: BLE001
+        out["vs_measured_sustained"] = None
+    return out
+
+
 def result_line(args, n, impl, ms_total, clocks, extra: dict) -> dict:
     tp, pp, dp = LAYOUTS[n]
     gb = args.seqs_per_gpu * n
@@ -276,6 +295,7 @@ def result_line(args, n, impl, ms_total, clocks, extra: dict) -> dict:
             "l2": "inputs larger than L2 (14.5 GB of bf16 weights stream every step; no explicit flush)",
         },
     }
+    line["mfu"] = mfu_block(args, value, n)
     line.update(extra)
     if args.layers != 32 or args.seqs_per_gpu != SEQS_PER_GPU or args.layout:
         line["non_headline"] = "development knobs changed the model/batch; not the BASELINE config"
@@ -288,10 +308,21 @@ def result_line(args, n, impl, ms_total, clocks, extra: dict) -> dict:
 def run_reference(args: argparse.Namespace) -> None:
     rank, local, world, addr, port = dist_env()
     ref_root = REPO / "baseline" / "_ref"
-    if not (ref_root / "scaling").is_dir():
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed"}))
-        return
+    if not (ref_root / "scaling" / "__init__.py").is_file():
+        # (re)create the install from a reachable reference checkout: rank 0 installs, the others wait for it
+        sys.path.insert(0, str(REPO / "baseline"))
+        from install_reference import ensure_reference
+
+        why = ""
+        if local == 0:
+            ok, why = ensure_reference()
+        t0 = time.time()
+        while not (ref_root / "scaling" / "__init__.py").is_file() and local != 0 and time.time() - t0 < 120:
+            time.sleep(0.5)
+        if not (ref_root / "scaling" / "__init__.py").is_file():
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": why or "baseline/_ref is not installed"}))
+            return
     sys.path.insert(0, str(ref_root))
     for name in [m for m in sys.modules if m == "scaling" or m.startswith("scaling.")]:
         del sys.modules[name]

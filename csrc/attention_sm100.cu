@@ -402,11 +402,9 @@ extern "C" int sb_attention_fwd(const void* q, const void* k, const void* v, voi
   Params p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale_log2 = scale * 1.4426950408889634f, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.out = (__nv_bfloat16*)out, p.lse = lse;
-  static bool configured = false;
-  if (!configured) {
+  static sb::PerDeviceOnce once;
+  if (once.first())
     SB_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    configured = true;
-  }
   const int blocks = (T + 2 * BQ - 1) / (2 * BQ) * heads;
   attention_fwd_kernel<<<blocks, kThreads, kSmemBytes, stream>>>(mq, mk, mv, p);
   return (int)cudaGetLastError();
@@ -944,13 +942,12 @@ extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, 
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale = scale, p.scale_log2 = scale * kLog2e, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
   p.dq = (__nv_bfloat16*)dq, p.dk = (__nv_bfloat16*)dk, p.dv = (__nv_bfloat16*)dv;
-  static bool configured = false;
+  static sb::PerDeviceOnce once;
   static bool separate = false;  // SCALING_B200_ATTN_BWD_SEPARATE=1: two launches (dK/dV, then dQ), for A/B timing
-  if (!configured) {
+  if (once.first()) {
     SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
     const char* e = getenv("SCALING_B200_ATTN_BWD_SEPARATE");
     separate = e && e[0] == '1';
-    configured = true;
   }
   // dK/dV blocks: K/V tiles stationary (128-row boxes), Q/dO streamed (64-row boxes); dQ blocks: the other way round
   CUtensorMap kq, kdo, kk, kv_, qq, qdo, qk, qv;

@@ -1,9 +1,12 @@
 // Native blend-index builder: the C++ equivalent of the Rust `blended_dataset_loop.sample`
 // wheel the reference calls from core/data/blended_dataset.py:316-329.
 //
-// Rule (Python spec of the loop: tfm/data/legacy_blended_dataset.py:214-229): repeatedly emit one sample from the
-// dataset whose sampled/target ratio is lowest (ties -> lowest dataset index), until every dataset has delivered its
-// target count.  Instead of an O(N·D) argmin scan this keeps a binary heap keyed on the exact rational
+// Rule: repeatedly emit one sample from the dataset whose sampled/target ratio is lowest (ties -> lowest dataset
+// index), until EVERY dataset has delivered its target count.  The reference's pure-Python variant of the loop
+// (tfm/data/legacy_blended_dataset.py:214-229) applies the same rule but stops when the FIRST dataset is exhausted;
+// the wheel's contract is "run to exhaustion" (the blended length equals the sum of the targets,
+// tests/transformer/test_blended_dataset.py:58), which is what this routine implements — the legacy output is a
+// prefix of it (tests/test_core_units_cpu.py::test_blend_index_extends_the_legacy_python_loop).  Instead of an O(N·D) argmin scan this keeps a binary heap keyed on the exact rational
 // sampled/target (compared by cross multiplication in 128-bit integers, so there is no floating-point tie noise):
 // O(N log D).
 #include <stdint.h>

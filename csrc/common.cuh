@@ -17,6 +17,18 @@
 
 namespace sb {
 
+// "first use on this device" latch for per-device set-up such as cudaFuncSetAttribute (one table per call site)
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool first() {
+    int d = 0;
+    cudaGetDevice(&d);
+    const bool f = !done[d & 63];
+    done[d & 63] = true;
+    return f;
+  }
+};
+
 // ---------------------------------------------------------------------------------------------
 // address helpers
 // ---------------------------------------------------------------------------------------------

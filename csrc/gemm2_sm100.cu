@@ -69,7 +69,6 @@ struct Params {
   // [r·rs_seq_per_rank, (r+1)·rs_seq_per_rank) of every batch item (Megatron sequence parallelism).  A 256-row tile lies
   // inside one rank's range; it is pushed to and reduced by that owner only, and D is the owner's compact [b·s/tp, N].
   int rs_seq, rs_seq_per_rank;
-  int debug;                      // timing experiments only (SB_AR_DEBUG): 1 no remote data, 2 wait own flags only, 4 no reduce
   uint32_t flag_slot;             // u32 flags per sender slot
   unsigned long long slot_bytes;  // bytes per sender slot
   uint8_t* ar_data[kMaxTP];       // rank r's workspace (this call's parity) as mapped into this process
@@ -415,11 +414,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       int tm, tn;
       tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
       const uint32_t ct = (uint32_t)t * 2 + rank;
-      if (p.debug & 4) continue;
       if (p.rs_seq > 0 && rs_owner(p, tm * BM) != p.tp_rank) continue;  // another rank reduces this tile
       if (lane == 0) {
-        for (int s = 0; s < p.tp_size; ++s)
-          if (!(p.debug & 2) || s == p.tp_rank) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
+        for (int s = 0; s < p.tp_size; ++s) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
       }
       __syncwarp();
       const uint8_t* base = mine + ((size_t)ct * 4 + rw) * kSlabBytes;
@@ -513,8 +510,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             bulk_store_s2g(p.ar_data[rs_tile_owner] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
           } else {
             for (int r = 0; r < p.tp_size; ++r)
-              if (!(p.debug & 1) || r == p.tp_rank)
-                bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
+              bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
           }
           bulk_commit();
         }
@@ -753,27 +749,21 @@ static int num_sms() {
   return n;
 }
 
-// Persistent workspace of the split-K tail (one per device; the library serialises its use on the launching stream —
-// GEMMs of this library issued concurrently on several streams of one device must disable splitting).
+// Workspace of the split-K tail: caller-owned (the library allocates nothing), registered once per device with
+// sb_gemm2_set_split_workspace.  Without a registered workspace the tail is simply not split.  The library serialises
+// its use on the launching stream — GEMMs issued concurrently on several streams of one device must disable splitting.
 struct SplitWorkspace {
   float* ws = nullptr;
   unsigned int* counters = nullptr;
 };
+static SplitWorkspace g_split_ws[64];
+static size_t split_partial_bytes() { return (size_t)num_sms() * kCtaAccFloats * sizeof(float); }
+static size_t split_counter_bytes() { return (size_t)num_sms() * sizeof(unsigned int); }
 static SplitWorkspace* split_workspace() {
-  static SplitWorkspace table[64];
   int dev = 0;
   cudaGetDevice(&dev);
-  SplitWorkspace& w = table[dev & 63];
-  if (!w.ws) {
-    const size_t partial_bytes = (size_t)num_sms() * kCtaAccFloats * sizeof(float);
-    const size_t counter_bytes = (size_t)num_sms() * sizeof(unsigned int);
-    void* base = nullptr;
-    if (cudaMalloc(&base, partial_bytes + counter_bytes) != cudaSuccess) return nullptr;
-    cudaMemset(static_cast<char*>(base) + partial_bytes, 0, counter_bytes);
-    w.ws = static_cast<float*>(base);
-    w.counters = reinterpret_cast<unsigned int*>(static_cast<char*>(base) + partial_bytes);
-  }
-  return &w;
+  SplitWorkspace& w = g_split_ws[dev & 63];
+  return w.ws ? &w : nullptr;
 }
 static bool split_enabled() {
   static int on = -1;
@@ -787,12 +777,10 @@ static bool split_enabled() {
 template <int AM, int BMj, int EPI, typename OutT>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaStream_t stream, int max_ctas) {
   auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;  // the attribute is per device
+  if (once.first())
     SB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)(EPI == kAllReduce ? kArSmemBytes : kSmemBytes)));
-    configured = true;
-  }
   const int tiles = p.tiles_m * p.tiles_n;
   int width = num_sms() / 2;  // clusters the machine runs at once
   if (max_ctas > 0 && width > max_ctas / 2) width = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
@@ -829,6 +817,24 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaS
 }  // namespace sb
 
 using namespace sb::gemm2;
+
+// Split-K tail workspace (see SplitWorkspace): bytes needed on the current device, and registration of a caller-owned,
+// 16-byte aligned buffer of at least that size for the current device.  The words behind the fp32 partials are arrival
+// counters and must be zero at registration (the kernels leave them zero).  Pass NULL to unregister.
+extern "C" long long sb_gemm2_split_workspace_bytes() { return (long long)(split_partial_bytes() + split_counter_bytes()); }
+extern "C" int sb_gemm2_set_split_workspace(void* base, unsigned long long bytes) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  SplitWorkspace& w = g_split_ws[dev & 63];
+  if (base == nullptr) {
+    w.ws = nullptr, w.counters = nullptr;
+    return 0;
+  }
+  if (bytes < split_partial_bytes() + split_counter_bytes() || (reinterpret_cast<uintptr_t>(base) & 15)) return -2;
+  w.ws = static_cast<float*>(base);
+  w.counters = reinterpret_cast<unsigned int*>(static_cast<char*>(base) + split_partial_bytes());
+  return 0;
+}
 
 // Same contract as sb_gemm_bf16 (gemm_sm100.cu), computed by CTA pairs (cta_group::2).
 extern "C" int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
@@ -910,14 +916,6 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
   p.tiles_n = (N + BN - 1) / BN;
   const unsigned long long cta_tiles = 2ull * p.tiles_m * p.tiles_n;
   if (cta_tiles * kCtaTileBytes > slot_bytes || cta_tiles > flag_slot) return -21;
-  {
-    static int dbg = -1;
-    if (dbg < 0) {
-      const char* e = getenv("SB_AR_DEBUG");
-      dbg = e ? atoi(e) : 0;
-    }
-    p.debug = dbg;
-  }
   p.rs_seq = rs_seq, p.rs_seq_per_rank = rs_seq > 0 ? rs_seq / tp_size : 0;
   p.tp_rank = tp_rank, p.tp_size = tp_size, p.epoch = epoch, p.flag_slot = flag_slot, p.slot_bytes = slot_bytes;
   for (int r = 0; r < tp_size; ++r) {

@@ -354,11 +354,9 @@ static int num_sms() {
 template <int AM, int BMj, int EPI, typename OutT>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream, int max_ctas) {
   auto kern = gemm_kernel<AM, BMj, EPI, OutT>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;
+  if (once.first())
     SB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    configured = true;
-  }
   int tiles = p.tiles_m * p.tiles_n;
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;

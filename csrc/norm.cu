@@ -211,16 +211,45 @@ __global__ void __launch_bounds__(kThreads) norm_bwd_kernel(const T* __restrict_
   }
 }
 
-// column-reduce the per-CTA partials; accumulate==1 adds to the existing gradient (main-grad semantics)
+// column-reduce the per-CTA partials; accumulate==1 adds to the existing gradient (main-grad semantics).
+// One CTA owns 32 adjacent columns: lane = column (128-byte coalesced rows), the 32 warps stride over the partial rows,
+// then a fixed-order shared-memory tree sums the 32 warp totals, so the result is deterministic and the `parts`
+// (up to 592) loads per column are spread over 32 warps instead of one serial loop.
+constexpr int kReduceWarps = 32;
 template <typename G>
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, G* __restrict__ grad, int parts, int cols,
-                                       int accumulate) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+__global__ void __launch_bounds__(32 * kReduceWarps)
+    reduce_partials_kernel(const float* __restrict__ partial, G* __restrict__ grad, int parts, int cols, int accumulate) {
+  __shared__ float tile[kReduceWarps][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
   float s = 0.f;
-  for (int p = 0; p < parts; ++p) s += partial[(size_t)p * cols + c];
-  if (accumulate) s += (float)grad[c];
-  grad[c] = (G)s;
+  if (c < cols) {
+#pragma unroll 4
+    for (int p = warp; p < parts; p += kReduceWarps) s += partial[(size_t)p * cols + c];
+  }
+  tile[warp][lane] = s;
+  __syncthreads();
+  if (warp == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kReduceWarps; ++w) t += tile[w][lane];
+    if (accumulate) t += (float)grad[c];
+    grad[c] = (G)t;
+  }
+}
+
+// launches the weight (and, for LayerNorm, bias) gradient reductions over `grid` partial rows
+template <typename T>
+static void launch_reduce(const float* pw, const float* pb, void* dw, void* db, int grid, int cols, int rms,
+                          int grad_fp32, int accumulate, cudaStream_t st) {
+  const int rb = (cols + 31) / 32, th = 32 * kReduceWarps;
+  if (grad_fp32) {
+    reduce_partials_kernel<float><<<rb, th, 0, st>>>(pw, (float*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<float><<<rb, th, 0, st>>>(pb, (float*)db, grid, cols, accumulate);
+  } else {
+    reduce_partials_kernel<T><<<rb, th, 0, st>>>(pw, (T*)dw, grid, cols, accumulate);
+    if (!rms && db) reduce_partials_kernel<T><<<rb, th, 0, st>>>(pb, (T*)db, grid, cols, accumulate);
+  }
 }
 
 static int grid_for(int rows) {
@@ -253,14 +282,7 @@ static int bwd(const void* dy, const void* x, const void* w, const float* mean, 
   float* pb = scratch + (size_t)grid * cols;
   k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,
                                  rows, cols);
-  const int rb = (cols + 255) / 256;
-  if (grad_fp32) {
-    reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pw, (float*)dw, grid, cols, accumulate);
-    if (!rms && db) reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pb, (float*)db, grid, cols, accumulate);
-  } else {
-    reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pw, (T*)dw, grid, cols, accumulate);
-    if (!rms && db) reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pb, (T*)db, grid, cols, accumulate);
-  }
+  launch_reduce<T>(pw, pb, dw, db, grid, cols, rms, grad_fp32, accumulate, st);
   return (int)cudaGetLastError();
 }
 
@@ -306,7 +328,7 @@ extern "C" int sb_norm_bwd(const void* dy, const void* x, const void* w, const f
 // plugin running inside another framework's allocator lock, or a C caller that simply has no allocator to offer.
 // Such callers cannot give sb_norm_bwd the fp32 scratch it needs for the per-CTA weight-gradient partials, so
 // this variant brings its own: a fixed array that lives in the library image.  Every GPU that loads the
-// library carries these kNoAllocScratchFloats * 4 bytes (4.75 MiB) until the process exits.
+// library carries these kNoAllocScratchFloats * 4 bytes (148 * 8192 * 4 = 4 849 664 B, 4.625 MiB) until the process exits.
 //
 // The price of a fixed array is a fixed limit: the launch uses at most kNoAllocGrid CTAs, and
 // grid * cols * (rms ? 1 : 2) floats must fit, i.e. cols <= 8192 for RMSNorm and cols <= 4096 for LayerNorm.
@@ -315,7 +337,8 @@ extern "C" int sb_norm_bwd(const void* dy, const void* x, const void* w, const f
 // In host code the name `g_noalloc_scratch` is only a handle for the symbol, not a pointer the GPU can use, so the
 // device address is looked up with cudaGetSymbolAddress once per device (with that device current) and cached.
 // That lookup happens inside the first call made on each device; make that first call outside of any stream
-// capture.  All calls share the one array and it keeps whatever the previous call left in it.  Nothing in it has
+// capture.  The address is resolved for the CURRENT device: the device that is current at the call must be the one
+// that owns `st` and the buffers.  All calls share the one array and it keeps whatever the previous call left in it.  Nothing in it has
 // to start at zero — every slot the reduction reads was written earlier in the same call — but two calls that
 // overlap on the GPU (different streams, no dependency) would overwrite each other's partials: serialise them.
 // ---------------------------------------------------------------------------------------------------------------
@@ -366,14 +389,7 @@ static int bwd_noalloc(const void* dy, const void* x, const void* w, const float
   float* pb = scratch + (size_t)grid * cols;
   k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,
                                  rows, cols);
-  const int rb = (cols + 255) / 256;
-  if (grad_fp32) {
-    reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pw, (float*)dw, grid, cols, accumulate);
-    if (!rms && db) reduce_partials_kernel<float><<<rb, 256, 0, st>>>(pb, (float*)db, grid, cols, accumulate);
-  } else {
-    reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pw, (T*)dw, grid, cols, accumulate);
-    if (!rms && db) reduce_partials_kernel<T><<<rb, 256, 0, st>>>(pb, (T*)db, grid, cols, accumulate);
-  }
+  launch_reduce<T>(pw, pb, dw, db, grid, cols, rms, grad_fp32, accumulate, st);
   return (int)cudaGetLastError();
 }
 
@@ -390,7 +406,7 @@ extern "C" const char* sb_norm_bwd_noalloc_strerror(int code) {
   using namespace sb::norm;
   switch (code) {
     case 0: return "success";
-    case kNoAllocBadArgument: return "sb_norm_bwd_noalloc: cols must be a positive multiple of 8 and rows positive";
+    case kNoAllocBadArgument: return "sb_norm_bwd_noalloc: cols must be a positive multiple of 8";
     case kNoAllocBadDtype: return "sb_norm_bwd_noalloc: dtype must be 0 (bf16), 1 (fp32) or 2 (fp16)";
     case kNoAllocTooLarge:
       return "sb_norm_bwd_noalloc: problem too large for the built-in scratch (cols <= 8192 for RMSNorm, <= 4096 for "
@@ -407,7 +423,8 @@ extern "C" int sb_norm_bwd_noalloc(const void* dy, const void* x, const void* w,
                                    const void* dres, void* dx, void* dw, void* db, int grad_fp32, int accumulate,
                                    int rows, int cols, int rms, int dtype, cudaStream_t st) {
   using namespace sb::norm;
-  if (rows <= 0 || cols <= 0 || cols % 8) return kNoAllocBadArgument;
+  if (rows <= 0) return 0;  // nothing to do, like sb_norm_bwd
+  if (cols <= 0 || cols % 8) return kNoAllocBadArgument;
   if (cols > sb_norm_bwd_noalloc_max_cols(rms)) return kNoAllocTooLarge;
   if (dtype == 0)
     return bwd_noalloc<__nv_bfloat16>(dy, x, w, mean, rstd, dres, dx, dw, db, grad_fp32, accumulate, rows, cols, rms, st);

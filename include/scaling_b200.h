@@ -26,12 +26,18 @@ int sb_gemm_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M,
 
 /* 2-CTA (tcgen05 cta_group::2, 256x256 tiles) variants with the same contracts; the Python layer selects them for
  * M >= 256 and N >= 128.  The last, partial wave of tiles is split along K when each part keeps >= 112 k-blocks
- * (fp32 partials meet in a library-owned workspace; disable with SCALING_B200_GEMM_SPLITK=0).
+ * (fp32 partials meet in the caller-owned workspace registered with sb_gemm2_set_split_workspace; without one the
+ * tail is not split; disable with SCALING_B200_GEMM_SPLITK=0).
  * Reference counterpart: cuBLAS GEMM behind F.linear (core/nn/linear/column_parallel_linear.py:151). */
 int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
                   int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas, cudaStream_t st);
 int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
                          int ldh, int ldpre, int max_ctas, cudaStream_t st);
+/* Split-K tail workspace of the 2-CTA GEMMs: size for the current device, and registration (once per device, with that
+ * device current) of a caller-owned 16-byte aligned buffer of at least that size whose trailing counter words are
+ * zero.  GEMMs that split must then be issued on one stream at a time per device.  NULL unregisters. */
+long long sb_gemm2_split_workspace_bytes(void);
+int sb_gemm2_set_split_workspace(void* base, unsigned long long bytes);
 
 /* Fused tensor-parallel GEMM + all-reduce over NVLink peer memory: D = sum over ranks of op(A)·op(B) (+ bias), bf16,
  * bit-identical on every rank.  data_ptrs[r] / flag_ptrs[r]: rank r's symmetric workspace regions of this call's
@@ -95,7 +101,7 @@ int sb_norm_bwd(const void* dy, const void* x, const void* w, const float* mean,
 
 /* No counterpart in the reference.  sb_norm_bwd for callers that cannot allocate device memory (stream capture,
  * memory fully committed elsewhere, foreign allocator, plain C hosts): the fp32 partial buffer is a static array inside
- * the library (4.75 MiB per GPU that loads it) instead of a caller argument.  Limits: cols <= 8192 (RMSNorm) /
+ * the library (4.625 MiB per GPU that loads it; the current device must own the stream) instead of a caller argument.  Limits: cols <= 8192 (RMSNorm) /
  * 4096 (LayerNorm), else status -3.  The first call on each device resolves the array's device address — issue it
  * outside stream capture.  Calls share the array: do not overlap two of them on the GPU. */
 int sb_norm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,

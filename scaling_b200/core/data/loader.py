@@ -35,16 +35,23 @@ class RandomSampler:
     def __len__(self) -> int:
         return self.total_samples
 
+    def seed_current_epoch(self) -> None:
+        """Re-seed the dataset for the epoch `consumed_samples` lies in.  Called before a torch iterator is built:
+        worker processes copy the dataset when the iterator is created, i.e. before the sampler's first index."""
+        self.dataset.set_seed(seed=self.seed + self.consumed_samples // self.usable_total_samples, shuffle=self.shuffle)
+
     def __iter__(self) -> Iterator[int]:
-        while True:
-            epoch = self.consumed_samples // self.usable_total_samples
-            in_epoch = self.consumed_samples % self.usable_total_samples
-            self.dataset.set_seed(seed=self.seed + epoch, shuffle=self.shuffle)
-            start = in_epoch // self.dp
-            n_per_rank = self.usable_total_samples // self.dp
-            for i in range(start, n_per_rank):
-                self.consumed_samples += self.dp
-                yield i * self.dp + self.dp_rank
+        """ONE epoch (the rest of the current one after a resume).  The iterator ends at the epoch boundary so that
+        the torch DataLoader — and its worker processes, which hold their own copy of the dataset — is rebuilt with
+        the dataset re-seeded for the next epoch (`DataLoader.__next__` below)."""
+        epoch = self.consumed_samples // self.usable_total_samples
+        in_epoch = self.consumed_samples % self.usable_total_samples
+        self.dataset.set_seed(seed=self.seed + epoch, shuffle=self.shuffle)
+        start = in_epoch // self.dp
+        n_per_rank = self.usable_total_samples // self.dp
+        for i in range(start, n_per_rank):
+            self.consumed_samples += self.dp
+            yield i * self.dp + self.dp_rank
 
 
 class DataLoader:
@@ -61,10 +68,17 @@ class DataLoader:
             dataset, batch_size=topology.config.micro_batch_size, sampler=self.sampler, num_workers=num_workers,
             pin_memory=pin_memory and torch.cuda.is_available(), collate_fn=dataset.collate, drop_last=True, **kwargs,
         )
+        self.sampler.seed_current_epoch()
         self._it = iter(self.loader)
 
     def __iter__(self) -> "DataLoader":
         return self
 
     def __next__(self) -> Any:
-        return next(self._it)
+        try:
+            return next(self._it)
+        except StopIteration:
+            # epoch boundary: a fresh torch iterator forks fresh workers AFTER the sampler re-seeded the dataset
+            self.sampler.seed_current_epoch()
+            self._it = iter(self.loader)
+            return next(self._it)

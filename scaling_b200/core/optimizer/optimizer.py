@@ -309,6 +309,13 @@ class Optimizer(BaseOptimizer):
             return cache[li]
 
         loaded_any = False
+        # Start from the weights the model checkpoint just put into the arenas: a parameter without an entry in the
+        # optimizer files (frozen in the run that wrote them, files pruned, groups changed for finetuning) must keep
+        # its LOADED weight, not the construction-time master, and begins with zero moments.
+        for g in self.parameter_groups:
+            g.refresh_optimized_params(topo)
+            g.exp_avg.zero_()
+            g.exp_avg_sq.zero_()
         for g in self.parameter_groups:
             for p, m, o in zip(g.parameters_original, g.parameter_metas, g.offsets):
                 if m.layer_index is None or m.layer_index < 0:

@@ -61,8 +61,10 @@ _RET_LL = {
     "sb_attention_bwd_scratch_floats": [c_int, c_int],
     "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
     "sb_gemm2_allreduce_slot_bytes": [c_int, c_int],
+    "sb_gemm2_split_workspace_bytes": [],
 }
-_RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int]}
+_RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int],
+                     "sb_gemm2_set_split_workspace": [P, c_ulonglong]}
 
 
 def lib_path() -> Path:

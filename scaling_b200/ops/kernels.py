@@ -25,9 +25,33 @@ def set_gemm_impl(name: str) -> None:
     _GEMM_IMPL = name
 
 
-def _gemm_entry(M: int, N: int) -> str:
+_split_ws: dict[int, torch.Tensor] = {}
+
+
+def _ensure_split_workspace(device: torch.device) -> None:
+    """The 2-CTA GEMM's split-K tail parks fp32 partials in a workspace the CALLER owns (the library allocates nothing):
+    one zero-initialised buffer per device from torch's allocator, registered once and kept alive here."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx in _split_ws:
+        return
+    lib = _lib.load(required=True)
+    with torch.cuda.device(idx):
+        n = int(lib.sb_gemm2_split_workspace_bytes())
+        buf = torch.zeros(n, dtype=torch.uint8, device=torch.device("cuda", idx))
+        torch.cuda.current_stream().synchronize()  # zeros must have landed before any stream's first GEMM uses it
+        rc = lib.sb_gemm2_set_split_workspace(buf.data_ptr(), n)
+    if rc != 0:
+        raise RuntimeError(f"sb_gemm2_set_split_workspace failed with status {rc}")
+    _split_ws[idx] = buf
+
+
+def _gemm_entry(M: int, N: int, device: Optional[torch.device] = None) -> str:
     # tiny problems do not fill CTA pairs; keep them on the single-CTA kernel
-    return "sb_gemm2_bf16" if (_GEMM_IMPL == "2cta" and M >= 256 and N >= 128) else "sb_gemm_bf16"
+    if _GEMM_IMPL == "2cta" and M >= 256 and N >= 128:
+        if device is not None:
+            _ensure_split_workspace(device)
+        return "sb_gemm2_bf16"
+    return "sb_gemm_bf16"
 
 
 def _scratch_buf(device: torch.device, n_floats: int, tag: str) -> torch.Tensor:
@@ -84,7 +108,7 @@ def gemm(
         assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
     try:
         call(
-            _gemm_entry(M, N), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
+            _gemm_entry(M, N, a.device), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
             DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
         )
     except RuntimeError as e:
@@ -164,6 +188,8 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True)
     assert F % 8 == 0 and x.stride(0) % 8 == 0 and w_gate_up.stride(0) % 8 == 0
     h = torch.empty((M, F), dtype=torch.bfloat16, device=x.device)
     pre = torch.empty((M, 2 * F), dtype=torch.bfloat16, device=x.device) if keep_pre else None
+    if _GEMM_IMPL == "2cta" and M >= 256:
+        _ensure_split_workspace(x.device)
     call(
         "sb_gemm2_swiglu_bf16" if (_GEMM_IMPL == "2cta" and M >= 256) else "sb_gemm_swiglu_bf16", ptr(x), ptr(w_gate_up), ptr(h), ptr(pre), M, F, K, x.stride(0), w_gate_up.stride(0), F,
         2 * F, 0,

@@ -13,6 +13,7 @@ from pydantic import Field, ValidationError
 
 from scaling_b200.core import (
     BaseConfig,
+    BaseDataset,
     FileDataset,
     LearningRateScheduler,
     LearningRateSchedulerConfig,
@@ -331,6 +332,65 @@ def test_resumable_sampler_covers_every_index_once(dp, mbs, n):
     it = iter(RandomSampler(ds, seed=5, consumed_samples=usable, topology=topo(0)))
     next(it)
     assert ds.seeds[-1] == 6
+
+
+class _SeededItems(BaseDataset):
+    """Items carry the seed their (possibly worker-side) dataset copy was last given."""
+
+    def __init__(self, n):
+        self.n = n
+        super().__init__(seed=0)
+
+    def ident(self):
+        return "seeded"
+
+    def __len__(self):
+        return self.n
+
+    def set_seed(self, seed, shuffle=True):
+        self.seed = seed
+
+    def __getitem__(self, i):
+        return (i, self.seed)
+
+    def collate(self, batch):
+        return batch
+
+    @staticmethod
+    def sync_batch_to_model_parallel(topology, batch):
+        return batch
+
+
+@pytest.mark.parametrize("workers", [0, 1])
+def test_loader_reseeds_worker_copies_at_every_epoch(workers):
+    """The torch iterator (and with it the worker processes' dataset copies) is rebuilt at the epoch boundary, after
+    the dataset was re-seeded with seed + epoch (reference: core/data/dataloader.py:56-96)."""
+    from scaling_b200.core.data.loader import DataLoader
+
+    topo = Topology(TopologyConfig(model_parallel_size=1, pipe_parallel_size=1, data_parallel_size=1, micro_batch_size=2,
+                                   gradient_accumulation_steps=1, global_rank=0))
+    loader = DataLoader(seed=10, consumed_samples=0, dataset=_SeededItems(6), topology=topo, num_workers=workers,
+                        pin_memory=False)
+    seeds = [[seed for _, seed in next(loader)] for _ in range(9)]  # three epochs of three batches
+    assert seeds == [[10, 10]] * 3 + [[11, 11]] * 3 + [[12, 12]] * 3
+    assert loader.sampler.consumed_samples == 18
+
+
+def test_blend_index_extends_the_legacy_python_loop():
+    """The legacy Python loop (transformer/data/legacy_blended_dataset.py:214-229) stops as soon as the FIRST dataset
+    has delivered its target; the native index (like the Rust wheel, whose blended length equals the sum of the parts,
+    tests/transformer/test_blended_dataset.py:58) keeps going until every dataset has.  Same rule, so the legacy
+    output is a prefix of ours."""
+    counts = np.array([5, 9, 2, 7], dtype=np.int64)
+    sampled = np.zeros(len(counts), dtype=np.int64)
+    legacy = []
+    while (sampled < counts).all():
+        d = int((sampled / counts).argmin())
+        legacy.append([d, int(sampled[d])])
+        sampled[d] += 1
+    ours = blend_index(counts)
+    assert len(ours) == counts.sum() > len(legacy) > 0
+    assert ours[:len(legacy)].tolist() == legacy
 
 
 # ---------------------------------------------------------------------------------------------------- logging

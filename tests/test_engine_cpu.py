@@ -209,3 +209,49 @@ def test_profiler_output_feeds_the_schedule_simulator(tmp_path):
     assert summary["duration"] > 0 and len(summary["stages"]) == 2 and 0 <= summary["idle_percent"] < 100
     assert sim.visualize() is not None
     assert PipelineScheduleTrain.visualize_profile(out) is not None
+
+
+def _missing_entry_worker(rank, world_size, master_port, save_dir):
+    """Loads a checkpoint whose optimizer files lack one parameter and steps once: that parameter must continue from
+    its LOADED weight (master refreshed from the model files), not from the fresh construction-time master."""
+    import torch
+
+    from scaling_b200.core import BaseTrainer, Optimizer, OptimizerParamGroup, OptimizerParamGroupConfig, ParallelModule, Topology
+    from tests.minimal import (MinimalConfig, MinimalContext, MinimalDataset, layer_specs, loss_function,
+                               metrics_aggregation_fn)
+
+    cfg = base_config(1, 1, 1, zero=True, iters=3, load_dir=save_dir)
+    cfg["topology"] = dict(cfg["topology"], world_size=world_size, global_rank=rank, local_slot=rank)
+    cfg["trainer"]["seed"] = 7  # a different seed: construction-time weights differ from the saved ones
+    config = MinimalConfig.from_dict(cfg)
+    topology = Topology(config.topology)
+    context = MinimalContext(config=config, topology=topology)
+    context.initialize(master_addr="127.0.0.1", master_port=str(master_port), seed=config.trainer.seed)
+    model = ParallelModule(layer_specs(config, topology), topology=topology, profiler_config=config.profiler)
+    named = model.named_parameters_with_meta()
+    group = OptimizerParamGroup(named, OptimizerParamGroupConfig(name="all", weight_decay=0.0,
+                                                                 learning_rate_scheduler=config.learning_rate_scheduler))
+    optimizer = Optimizer(config.optimizer, [group], topology)
+    trainer = BaseTrainer(config=config.trainer, context=context, parallel_module=model, optimizer=optimizer,
+                          dataset=MinimalDataset(seed=1), sync_batch_to_model_parallel=MinimalDataset.sync_batch_to_model_parallel,
+                          loss_function=loss_function, metrics_aggregation_fn=metrics_aggregation_fn)
+    victim = next(p for n, p in model.named_parameters() if n.endswith("down.weight"))
+    saved = torch.load(f"{save_dir}/global_step2/model_state_layer_1_HiddenLayer.pt", weights_only=False)["down.weight"]
+    assert torch.equal(victim.detach().cpu(), saved)
+    trainer.train_step()
+    # one AdamW step at lr 0.01 moves every element by at most ~lr; the fresh random master would be far away
+    return float((victim.detach().cpu() - saved).abs().max())
+
+
+def test_optimizer_load_keeps_loaded_weight_for_parameter_without_state(tmp_path):
+    import torch
+
+    dist_launcher(run_minimal, 1, config_dict=base_config(1, 1, 1, zero=True, iters=2, save_dir=str(tmp_path), save_interval=2))
+    f = tmp_path / "global_step2" / "optimizer_state_layer_1.pt"
+    sd = torch.load(f, weights_only=False)
+    dropped = [k for k in sd["parameters"] if "down.weight" in k]
+    assert len(dropped) == 1
+    del sd["parameters"][dropped[0]]
+    torch.save(sd, f)
+    drift = dist_launcher(_missing_entry_worker, 1, save_dir=str(tmp_path))[0]
+    assert drift < 0.05, drift

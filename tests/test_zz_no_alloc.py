@@ -48,12 +48,14 @@ def _rel(a, b):
     return float((a - b).norm() / (b.norm() + 1e-12))
 
 
-@pytest.mark.parametrize("rms,dtype,code", [(1, torch.bfloat16, 0), (0, torch.float32, 1)])
-def test_noalloc_matches_regular_entry_point_twice(lib, rms, dtype, code):
+@pytest.mark.parametrize("rms,dtype,code,with_dres,accumulate", [
+    (1, torch.bfloat16, 0, False, 0), (0, torch.float32, 1, False, 0),
+    (1, torch.float16, 2, True, 1), (0, torch.bfloat16, 0, True, 1)])
+def test_noalloc_matches_regular_entry_point_twice(lib, rms, dtype, code, with_dres, accumulate):
     torch.manual_seed(0)
     dev = "cuda"
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
     for call, (rows, cols) in enumerate([(1000, 4096), (333, 2048)]):
         x = torch.randn(rows, cols, device=dev, dtype=dtype)
         dy = torch.randn(rows, cols, device=dev, dtype=dtype)
@@ -67,15 +69,18 @@ def test_noalloc_matches_regular_entry_point_twice(lib, rms, dtype, code):
             rstd = torch.rsqrt(xf.var(-1, unbiased=False) + 1e-5)
         # everything the two calls write is allocated up front by the caller; the calls themselves allocate nothing
         dx_ref, dx_new = torch.empty_like(x), torch.empty_like(x)
-        dw_ref, dw_new = torch.zeros(cols, device=dev), torch.zeros(cols, device=dev)
-        db_ref, db_new = torch.zeros(cols, device=dev), torch.zeros(cols, device=dev)
+        # with accumulate=1 the gradients are added to what the buffers already hold (main-grad semantics)
+        dw0, db0 = torch.randn(cols, device=dev), torch.randn(cols, device=dev)
+        dw_ref, dw_new = dw0.clone(), dw0.clone()
+        db_ref, db_new = db0.clone(), db0.clone()
+        dres = torch.randn(rows, cols, device=dev, dtype=dtype) if with_dres else None  # gradient of the residual branch
         scratch = torch.empty(lib.sb_norm_bwd_scratch_floats(rows, cols, rms), device=dev, dtype=torch.float32)
-        rc = lib.sb_norm_bwd(_ptr(dy), _ptr(x), _ptr(w), _ptr(mean), _ptr(rstd), None, _ptr(dx_ref), _ptr(dw_ref),
-                             None if rms else _ptr(db_ref), 1, 0, _ptr(scratch), rows, cols, rms, code, stream)
+        rc = lib.sb_norm_bwd(_ptr(dy), _ptr(x), _ptr(w), _ptr(mean), _ptr(rstd), _ptr(dres), _ptr(dx_ref), _ptr(dw_ref),
+                             None if rms else _ptr(db_ref), 1, accumulate, _ptr(scratch), rows, cols, rms, code, stream)
         assert rc == 0
         before = torch.cuda.memory_allocated()
-        rc = lib.sb_norm_bwd_noalloc(_ptr(dy), _ptr(x), _ptr(w), _ptr(mean), _ptr(rstd), None, _ptr(dx_new), _ptr(dw_new),
-                                     None if rms else _ptr(db_new), 1, 0, rows, cols, rms, code, stream)
+        rc = lib.sb_norm_bwd_noalloc(_ptr(dy), _ptr(x), _ptr(w), _ptr(mean), _ptr(rstd), _ptr(dres), _ptr(dx_new), _ptr(dw_new),
+                                     None if rms else _ptr(db_new), 1, accumulate, rows, cols, rms, code, stream)
         assert rc == 0, lib.sb_norm_bwd_noalloc_strerror(rc).decode()
         torch.cuda.synchronize()
         assert torch.cuda.memory_allocated() == before
@@ -84,6 +89,12 @@ def test_noalloc_matches_regular_entry_point_twice(lib, rms, dtype, code):
         if not rms:
             assert _rel(db_new, db_ref) < tol, (call, _rel(db_new, db_ref))
         assert torch.isfinite(dw_new).all()
+
+
+def test_noalloc_empty_problem_is_a_no_op_like_the_regular_entry_point(lib):
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert lib.sb_norm_bwd_noalloc(None, None, None, None, None, None, None, None, None, 1, 0, 0, 4096, 1, 0, stream) == 0
+    assert lib.sb_norm_bwd(None, None, None, None, None, None, None, None, None, 1, 0, None, 0, 4096, 1, 0, stream) == 0
 
 
 def test_noalloc_refuses_oversized_problems(lib):
