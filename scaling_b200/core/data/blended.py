@@ -13,7 +13,7 @@ import hashlib
 import json
 import time
 from pathlib import Path
-from typing import Any, Generic, List, Optional, Sequence
+from typing import Any, Generic, List, Optional, Sequence, TypeVar
 
 import numpy as np
 import torch
@@ -22,6 +22,9 @@ from pydantic import Field
 from ..config import BaseConfig
 from ..logging import logger
 from .base import BaseDataset, BaseDatasetBatchBeforeSyncGeneric, BaseDatasetBatchGeneric, BaseDatasetItemGeneric
+
+# fourth type parameter of BaseBlendedDataset: the type of the blended member datasets (reference blended_dataset.py:128-140)
+BaseDatasetGeneric = TypeVar("BaseDatasetGeneric", bound=BaseDataset)
 
 
 class BlendedDatasetConfig(BaseConfig):
@@ -90,7 +93,8 @@ def blend_index(counts: np.ndarray) -> np.ndarray:
 
 
 class BaseBlendedDataset(BaseDataset[BaseDatasetItemGeneric, BaseDatasetBatchBeforeSyncGeneric, BaseDatasetBatchGeneric],
-                         Generic[BaseDatasetItemGeneric, BaseDatasetBatchBeforeSyncGeneric, BaseDatasetBatchGeneric]):
+                         Generic[BaseDatasetItemGeneric, BaseDatasetBatchBeforeSyncGeneric, BaseDatasetBatchGeneric,
+                                 BaseDatasetGeneric]):
     def __init__(self, seed: int, config: BlendedDatasetConfig, datasets: Sequence[BaseDataset], shuffle: bool = True):
         assert len(datasets) > 0, "at least one dataset is needed"
         self.config = config
@@ -177,10 +181,17 @@ class BaseBlendedDataset(BaseDataset[BaseDatasetItemGeneric, BaseDatasetBatchBef
         else:
             self.dataset_indices = np.memmap(f_bin, mode="r", order="C", dtype=np.dtype(meta["dtype"]), shape=shape)
         self.size = shape[0]
-        self.random_index = None
-        if self.config.shuffle_dataset_indices and shuffle:
+        # same observable state as the reference (blended_dataset.py:372-384): an in-memory index is permuted in place
+        # (random_index None), a memory-mapped one is read through random_index (identity when not shuffling)
+        do_shuffle = self.config.shuffle_dataset_indices and shuffle
+        if self.config.load_dataset_indices_to_memory:
+            if do_shuffle:
+                np.random.RandomState(seed=seed).shuffle(self.dataset_indices)
+            self.random_index = None
+        else:
             self.random_index = np.arange(self.size)
-            np.random.RandomState(seed=seed).shuffle(self.random_index)
+            if do_shuffle:
+                np.random.RandomState(seed=seed).shuffle(self.random_index)
 
     def __len__(self) -> int:
         return self.size

@@ -288,13 +288,13 @@ class FinetuningChatDataset(_FinetuningBase):
         return self._finish(self.data[index], loss_on_padding_eos=False)
 
 
-class FinetuningTextBlendedDataset(BaseBlendedDataset[FinetuningTextDatasetItem, TextDatasetBatch, TextDatasetBatch]):
+class FinetuningTextBlendedDataset(BaseBlendedDataset[FinetuningTextDatasetItem, TextDatasetBatch, TextDatasetBatch, FinetuningTextDataset]):
     @staticmethod
     def sync_batch_to_model_parallel(topology, batch):
         return _FinetuningBase.sync_batch_to_model_parallel(topology, batch)
 
 
-class FinetuningChatBlendedDataset(BaseBlendedDataset[FinetuningTextDatasetItem, TextDatasetBatch, TextDatasetBatch]):
+class FinetuningChatBlendedDataset(BaseBlendedDataset[FinetuningTextDatasetItem, TextDatasetBatch, TextDatasetBatch, FinetuningChatDataset]):
     @staticmethod
     def sync_batch_to_model_parallel(topology, batch):
         return _FinetuningBase.sync_batch_to_model_parallel(topology, batch)

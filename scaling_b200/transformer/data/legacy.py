@@ -319,7 +319,7 @@ def get_indexed_dataset_(data_prefix: str, data_impl: str, skip_warmup: bool):
 
 
 # ------------------------------------------------------------------------------------------------ legacy blend
-class LegacyBlendedDataset(BaseBlendedDataset[Any, TextDatasetBatchBeforeSync, TextDatasetBatch]):
+class LegacyBlendedDataset(BaseBlendedDataset[Any, TextDatasetBatchBeforeSync, TextDatasetBatch, Any]):
     def __init__(self, seed: int, config: BlendedDatasetConfig, datasets: Sequence[TextDataset], shuffle: bool = True):
         self.ep_maximum_dict: Optional[dict] = None
         self.weights: Optional[np.ndarray] = (np.asarray(config.weights, dtype=np.float64)

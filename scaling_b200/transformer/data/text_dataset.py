@@ -199,7 +199,7 @@ class TextDataset(BaseDataset[TextDatasetItem, TextDatasetBatchBeforeSync, TextD
                     builder.add(np.asarray(ids))
 
 
-class TextBlendedDataset(BaseBlendedDataset[TextDatasetItem, TextDatasetBatchBeforeSync, TextDatasetBatch]):
+class TextBlendedDataset(BaseBlendedDataset[TextDatasetItem, TextDatasetBatchBeforeSync, TextDatasetBatch, TextDataset]):
     @staticmethod
     def sync_batch_to_model_parallel(topology, batch):
         return TextDataset.sync_batch_to_model_parallel(topology, batch)

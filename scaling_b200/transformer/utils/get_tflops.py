@@ -85,9 +85,10 @@ class HardwareType(Enum):
 
     @classmethod
     def get_via_torch(cls) -> "HardwareType":
-        if not torch.cuda.is_available():
+        try:
+            name = torch.cuda.get_device_name()
+        except Exception:  # noqa: BLE001  (no CUDA device / driver)
             return cls.DEFAULT
-        name = torch.cuda.get_device_name()
         hw = cls.from_name(name)
         if hw == cls.DEFAULT:
             logger.warning(f"cuda device {name} does not match any known HardwareType")
