@@ -41,12 +41,13 @@ enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3 }
 // produces identical bits) and write the bf16 result (+ bias) to D.  The NVLink transfer of tile i overlaps the MMA of
 // tiles i+1.., the reduction of tile i overlaps both.
 constexpr int kMaxTP = 8;
-constexpr int kArThreads = 384;
-constexpr uint32_t kChunkBytes = 32 * 64 * 2;            // one staged sub-tile: 32 rows x 64 bf16
+constexpr int kArThreads = 512;                          // 4 control + 4 epilogue + 8 reducer warps
+constexpr int kArStages = 5;                             // one TMA stage less than the plain kernel: room for the slabs
+constexpr uint32_t kChunkBytes = 32 * 64 * 2;            // one sub-tile: 32 rows x 64 bf16
 constexpr uint32_t kSlabBytes = 4 * kChunkBytes;         // one epilogue warp's 32 x 256 slab
 constexpr uint32_t kCtaTileBytes = 4 * kSlabBytes;       // 128 x 256 bf16
-constexpr uint32_t kStagingBytes = 4 * 2 * kChunkBytes;  // 4 warps x double buffer
-constexpr uint32_t kArSmemBytes = kStages * (128 * BK * 2 * 2) + 256 + kStagingBytes + 1024;
+constexpr uint32_t kStagingBytes = 4 * kSlabBytes;       // every epilogue warp stages its whole slab (64 KiB per CTA)
+constexpr uint32_t kArSmemBytes = kArStages * (128 * BK * 2 * 2) + 256 + kStagingBytes + 1024;
 
 struct Params {
   int M, N, K;
@@ -69,6 +70,7 @@ struct Params {
   // [r·rs_seq_per_rank, (r+1)·rs_seq_per_rank) of every batch item (Megatron sequence parallelism).  A 256-row tile lies
   // inside one rank's range; it is pushed to and reduced by that owner only, and D is the owner's compact [b·s/tp, N].
   int rs_seq, rs_seq_per_rank;
+  unsigned long long* prof;       // optional [grid][8] globaltimer stamps of the phases (sb_gemm2_set_profile_buffer)
   uint32_t flag_slot;             // u32 flags per sender slot
   unsigned long long slot_bytes;  // bytes per sender slot
   uint8_t* ar_data[kMaxTP];       // rank r's workspace (this call's parity) as mapped into this process
@@ -175,6 +177,11 @@ SB_DEVICE unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
   return t;
 }
+// Phase stamp for tools/tpbench.py --profile: slot 0 kernel entry, 1 last accumulator ready, 2 last push complete,
+// 3 last flag published, 4 first / 5 last tile's flags seen by the reducer, 6 reducer done.
+SB_DEVICE void prof_stamp(unsigned long long* prof, int slot) {
+  if (prof) prof[(size_t)blockIdx.x * 8 + slot] = global_timer_ns();
+}
 // Spin until *flag == epoch.  A peer that never arrives (crashed rank) traps after 30 s instead of hanging the GPU.
 SB_DEVICE void wait_flag(const uint32_t* flag, uint32_t epoch) {
   if (ld_acquire_sys(flag) == epoch) return;
@@ -274,9 +281,10 @@ SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, int tail_tile, i
 template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kEpi == kAllReduce ? kArThreads : kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
+  constexpr int kNumStages = kEpi == kAllReduce ? kArStages : kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  Barriers* bars = reinterpret_cast<Barriers*>(smem + kStages * kStageBytes);
+  Barriers* bars = reinterpret_cast<Barriers*>(smem + kNumStages * kStageBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -291,9 +299,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    if (kEpi == kAllReduce) prof_stamp(p.prof, 0);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kStages; ++i) {
+    for (int i = 0; i < kNumStages; ++i) {
       mbar_init(&bars->full[i], 1);
       mbar_init(&bars->empty[i], 1);
     }
@@ -339,7 +348,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           } else {
             tma_load_2d_2sm(sb_, &tma_b, &bars->full[stage], k0, nb);
           }
-          if (++stage == kStages) {
+          if (++stage == kNumStages) {
             stage = 0;
             phase ^= 1;
           }
@@ -373,7 +382,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             umma_f16_ss_2sm(tmem_d, da, db, idesc, ((kb - w.kb0) | k) != 0);
           }
           umma_commit_2sm(&bars->empty[stage]);
-          if (++stage == kStages) {
+          if (++stage == kNumStages) {
             stage = 0;
             phase ^= 1;
           }
@@ -403,10 +412,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
         }
       }
+      prof_stamp(p.prof, 3);
     }
   } else if (kEpi == kAllReduce && warp >= 8) {
     // ===================== reducer warps (kAllReduce): sum the senders' partials of this CTA's tiles =====================
+    // eight warps: warp pair (2q, 2q+1) shares epilogue warp q's 32 x 256 slab, 128 columns each
     const int rw = warp - 8;
+    const int slab = rw >> 1, half = rw & 1;
     const uint8_t* mine = p.ar_data[p.tp_rank];
     const uint32_t* myflags = p.ar_flags[p.tp_rank];
     const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
@@ -417,13 +429,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       if (p.rs_seq > 0 && rs_owner(p, tm * BM) != p.tp_rank) continue;  // another rank reduces this tile
       if (lane == 0) {
         for (int s = 0; s < p.tp_size; ++s) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
+        if (rw == 0) {
+          if (t == cluster_id) prof_stamp(p.prof, 4);
+          if (t + num_clusters >= num_tiles) prof_stamp(p.prof, 5);
+        }
       }
       __syncwarp();
-      const uint8_t* base = mine + ((size_t)ct * 4 + rw) * kSlabBytes;
-      const int row0 = tm * BM + rank * 128 + rw * 32;
+      const uint8_t* base = mine + ((size_t)ct * 4 + slab) * kSlabBytes;
+      const int row0 = tm * BM + rank * 128 + slab * 32;
       const int n0 = tn * BN;
 #pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
+      for (int c4 = 2 * half; c4 < 2 * half + 2; ++c4) {
         uint4 xa[8], xb[8];
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -459,10 +475,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         }
       }
     }
+    if (rw == 0 && lane == 0) prof_stamp(p.prof, 6);
   } else if (kEpi == kAllReduce && warp >= 4) {
     // ===================== epilogue (kAllReduce): push bf16 partial tiles into every rank's workspace =====================
     const int ew = warp & 3;
-    uint8_t* staging = smem + kStages * kStageBytes + 256 + (uint32_t)ew * 2 * kChunkBytes;
+    uint8_t* slab_buf = smem + kNumStages * kStageBytes + 256 + (uint32_t)ew * kSlabBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
     int pending_ct = -1;
@@ -470,6 +487,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const uint32_t ct = (uint32_t)t * 2 + rank;
       mbar_wait(&bars->acc_full[acc], acc_phase);
       tc_fence_after();
+      if (ew == 0 && lane == 0 && t + num_clusters >= num_tiles) prof_stamp(p.prof, 1);
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
       const size_t slab_off = (size_t)p.tp_rank * p.slot_bytes + ((size_t)ct * 4 + ew) * kSlabBytes;
       int rs_tile_owner = 0;
@@ -478,11 +496,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
         rs_tile_owner = rs_owner(p, tm_ * BM);
       }
+      if (lane == 0) bulk_wait_read<0>();  // the previous tile's copies have drained the slab buffer
+      __syncwarp();
 #pragma unroll 1
       for (int c4 = 0; c4 < 4; ++c4) {
-        uint8_t* buf = staging + (c4 & 1) * kChunkBytes;
-        if (lane == 0) bulk_wait_read<1>();  // the copies that last read this buffer have drained it
-        __syncwarp();
+        uint8_t* buf = slab_buf + c4 * kChunkBytes;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t v[32];
@@ -498,26 +516,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             *reinterpret_cast<uint4*>(buf + lane * 128 + pos * 16) = o;
           }
         }
-        if (c4 == 3) {  // accumulator fully read: hand the TMEM stage back before the pushes
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          if (p.rs_seq > 0) {
-            bulk_store_s2g(p.ar_data[rs_tile_owner] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
-          } else {
-            for (int r = 0; r < p.tp_size; ++r)
-              bulk_store_s2g(p.ar_data[r] + slab_off + (size_t)c4 * kChunkBytes, buf, kChunkBytes);
-          }
-          bulk_commit();
-        }
       }
+      // accumulator fully read: hand the TMEM stage back before the pushes
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
+      fence_proxy_async_smem();
+      __syncwarp();
       if (lane == 0) {
-        if (pending_ct >= 0) {  // the previous tile's four groups have completed: hand it to the signal warp
-          bulk_wait<4>();
+        // ONE 16 KiB bulk copy per destination: the slab is contiguous in the workspace and in shared memory
+        if (p.rs_seq > 0) {
+          bulk_store_s2g(p.ar_data[rs_tile_owner] + slab_off, slab_buf, kSlabBytes);
+        } else {
+          for (int r = 0; r < p.tp_size; ++r) bulk_store_s2g(p.ar_data[r] + slab_off, slab_buf, kSlabBytes);
+        }
+        bulk_commit();
+        if (pending_ct >= 0) {  // the previous tile's group has completed: hand it to the signal warp
+          bulk_wait<1>();
           red_release_cta_smem_inc(&bars->pushed);
         }
         pending_ct = (int)ct;
@@ -530,6 +545,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     if (lane == 0 && pending_ct >= 0) {
       bulk_wait<0>();
       red_release_cta_smem_inc(&bars->pushed);
+      if (ew == 0) prof_stamp(p.prof, 2);
     }
   } else if (kEpi != kAllReduce && warp >= 4) {
     // ===================== epilogue (both CTAs, own 128 rows) =====================
@@ -886,6 +902,16 @@ extern "C" int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void*
   return launch<0, 0, kSwiGLU, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
 }
 
+// Optional phase profile of the fused collective kernels: a caller-owned buffer of grid x 8 u64 (148 x 8 is enough) for
+// the current device; NULL switches it off.  The kernels stamp %globaltimer at their phase boundaries (see prof_stamp).
+static unsigned long long* g_prof_buf[64] = {nullptr};
+extern "C" int sb_gemm2_set_profile_buffer(unsigned long long* buf) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  g_prof_buf[dev & 63] = buf;
+  return 0;
+}
+
 // Fused tensor-parallel GEMM + all-reduce: D = sum over ranks of op(A)·op(B) (+ bias), bf16, identical bits on every
 // rank.  `data_ptrs[r]` / `flag_ptrs[r]` are rank r's symmetric workspace regions (for this call's parity) as mapped
 // into this process; `epoch` must be unique per call on a workspace parity and equal on all ranks.  Replaces the
@@ -916,6 +942,11 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
   p.tiles_n = (N + BN - 1) / BN;
   const unsigned long long cta_tiles = 2ull * p.tiles_m * p.tiles_n;
   if (cta_tiles * kCtaTileBytes > slot_bytes || cta_tiles > flag_slot) return -21;
+  {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    p.prof = g_prof_buf[dev & 63];
+  }
   p.rs_seq = rs_seq, p.rs_seq_per_rank = rs_seq > 0 ? rs_seq / tp_size : 0;
   p.tp_rank = tp_rank, p.tp_size = tp_size, p.epoch = epoch, p.flag_slot = flag_slot, p.slot_bytes = slot_bytes;
   for (int r = 0; r < tp_size; ++r) {

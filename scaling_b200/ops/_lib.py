@@ -64,7 +64,7 @@ _RET_LL = {
     "sb_gemm2_split_workspace_bytes": [],
 }
 _RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int],
-                     "sb_gemm2_set_split_workspace": [P, c_ulonglong]}
+                     "sb_gemm2_set_split_workspace": [P, c_ulonglong], "sb_gemm2_set_profile_buffer": [P]}
 
 
 def lib_path() -> Path:

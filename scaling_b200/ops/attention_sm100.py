@@ -22,12 +22,39 @@ def sm100_attention_supported(q, k, v, cu_q, cu_k, causal, window, dropout_p) ->
             and k.stride(0) % 8 == 0 and v.stride(0) % 8 == 0)
 
 
-def segment_bounds(cu_seqlens: torch.Tensor, total: int) -> Tuple[torch.Tensor, torch.Tensor]:
-    """int32 [total] start / end (exclusive) of the sequence every packed token belongs to — device side, no sync."""
+_bounds_cache: "OrderedDict[tuple, tuple]" = None  # type: ignore[assignment]
+_BOUNDS_CACHE_ENTRIES = 16  # micro batches in flight under 1F1B keep their own entry
+
+
+def _compute_segment_bounds(cu_seqlens: torch.Tensor, total: int) -> Tuple[torch.Tensor, torch.Tensor]:
     cu = cu_seqlens.to(torch.int64)
     pos = torch.arange(total, device=cu.device)
     seg = torch.searchsorted(cu[1:].contiguous(), pos, right=True).clamp_(max=cu.numel() - 2)
     return cu[seg].to(torch.int32).contiguous(), cu[seg + 1].to(torch.int32).contiguous()
+
+
+def segment_bounds(cu_seqlens: torch.Tensor, total: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """int32 [total] start / end (exclusive) of the sequence every packed token belongs to — device side, no sync.
+
+    Every layer of a micro batch passes the SAME ``cu_seqlens`` tensor (it travels in the layer IO), so the result is
+    computed once per micro batch and looked up by tensor identity + version counter afterwards."""
+    global _bounds_cache
+    from collections import OrderedDict
+
+    if _bounds_cache is None:
+        _bounds_cache = OrderedDict()
+    key = (id(cu_seqlens), cu_seqlens._version, cu_seqlens.data_ptr(), total)
+    hit = _bounds_cache.get(key)
+    if hit is not None and hit[0]() is cu_seqlens:
+        _bounds_cache.move_to_end(key)
+        return hit[1], hit[2]
+    import weakref
+
+    start, end = _compute_segment_bounds(cu_seqlens, total)
+    _bounds_cache[key] = (weakref.ref(cu_seqlens), start, end)
+    while len(_bounds_cache) > _BOUNDS_CACHE_ENTRIES:
+        _bounds_cache.popitem(last=False)
+    return start, end
 
 
 def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float):
@@ -37,6 +64,23 @@ def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float):
     call("sb_attention_fwd", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, heads, k.shape[1],
          q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal))
     return out, lse
+
+
+_bwd_scratch_pool: dict = {}
+
+
+def _bwd_scratch(device: torch.device, T: int, heads: int) -> torch.Tensor:
+    """Persistent lse·log2e / delta scratch per (device, T, heads): zero-filled once (its padding is read but masked and
+    must stay finite), then reused by every backward call of that shape on the stream."""
+    key = (device.index, T, heads)
+    buf = _bwd_scratch_pool.get(key)
+    if buf is None:
+        lib = _lib.load(required=True)
+        if len(_bwd_scratch_pool) >= 8:
+            _bwd_scratch_pool.clear()
+        buf = torch.zeros(lib.sb_attention_bwd_scratch_floats(T, heads), dtype=torch.float32, device=device)
+        _bwd_scratch_pool[key] = buf
+    return buf
 
 
 def has_native_bwd() -> bool:
@@ -50,8 +94,7 @@ def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, sca
     dq = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     dk = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     dv = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
-    lib = _lib.load(required=True)
-    delta = torch.zeros(lib.sb_attention_bwd_scratch_floats(T, heads), dtype=torch.float32, device=q.device)
+    delta = _bwd_scratch(q.device, T, heads)
     call("sb_attention_bwd", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
          ptr(seg_start), ptr(seg_end), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
          launches=3)

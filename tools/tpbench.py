@@ -36,6 +36,44 @@ def timed(fn, iters=20, warm=5):
     return t.item()
 
 
+def phase_profile(comm, shapes, rank):
+    """In-kernel %globaltimer stamps of the fused kernel's phases (sb_gemm2_set_profile_buffer), per shape: microseconds
+    after the earliest CTA's kernel entry, median and max over CTAs of this rank."""
+    from scaling_b200.ops import _lib
+
+    lib = _lib.load(required=True)
+    buf = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+    names = ["entry", "last_acc_ready", "last_push_complete", "last_flag_published", "first_tile_flags_seen",
+             "last_tile_flags_seen", "reducer_done"]
+    out = {}
+    extra = dict(shapes)
+    extra["one_wave_attn_out"] = (1024, 4096, 2048, False)
+    for name, (M, N, Kd, b_mn) in extra.items():
+        a = (torch.randn(M, Kd, device="cuda") * 0.5).bfloat16()
+        b = (torch.randn((Kd, N) if b_mn else (N, Kd), device="cuda") * 0.05).bfloat16()
+        for _ in range(5):
+            K.gemm_allreduce(a, b, comm, b_mn=b_mn)
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        assert lib.sb_gemm2_set_profile_buffer(buf.data_ptr()) == 0
+        buf.zero_()
+        for _ in range(3):  # the third, steady-state call's stamps are the ones left in the buffer
+            K.gemm_allreduce(a, b, comm, b_mn=b_mn)
+        torch.cuda.synchronize()
+        lib.sb_gemm2_set_profile_buffer(None)
+        t = buf.view(148, 8).cpu().double()
+        live = t[:, 0] > 0
+        t = t[live]
+        t0 = t[:, 0].min()
+        rel = (t[:, :7] - t0) / 1e3
+        out[name] = {n: {"median": float(rel[:, i].median()), "max": float(rel[:, i].max())} for i, n in enumerate(names)}
+        out[name]["ctas"] = int(live.sum())
+        if rank == 0:
+            print("phases", name, json.dumps(out[name]), flush=True)
+    return out
+
+
 def main():
     rank = int(os.environ["RANK"])
     world = int(os.environ["WORLD_SIZE"])
@@ -95,8 +133,11 @@ def main():
                      "rel_err": err, "bit_identical": same}
         if rank == 0:
             print(name, json.dumps(res[name]), flush=True)
+    phases = phase_profile(comm, shapes, rank) if "--profile" in sys.argv else None
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
+        if phases is not None:
+            json.dump({"tp": tp, "phases_us": phases}, open(f"gpurun_out/tpbench_phases_tp{tp}.json", "w"), indent=1)
         json.dump({"tp": tp, "shapes": res, "ok": ok}, open(f"gpurun_out/tpbench_tp{tp}.json", "w"), indent=1)
         print("OK" if ok else "NUMERICS MISMATCH", flush=True)
     dist.barrier()
