@@ -257,6 +257,34 @@ __global__ void embedding_fwd_kernel(const long long* __restrict__ ids, const __
     *reinterpret_cast<uint4*>(out + (size_t)t * hidden + c) = v;
   }
 }
+// Vocab-parallel embedding forward with the tensor-parallel "sum" done by placement: every token's row
+// lives on exactly one rank, so that owner stores the row straight into the output buffer of every TP rank (NVLink peer
+// stores into symmetric memory) and nobody adds anything — no dense all-reduce of [b, s, h].  With seq_per_rank > 0
+// (sequence parallelism) the row goes only to the rank that owns the token's sequence position, at its compact row
+// b * seq_per_rank + s % seq_per_rank: the reduce-scatter along the sequence by placement.
+struct EmbPeers {
+  __nv_bfloat16* p[8];
+  int n;
+};
+__global__ void embedding_fwd_peers_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ W,
+                                           EmbPeers outs, int tokens, int hidden, long long vocab_start,
+                                           long long vocab_end, int seq, int seq_per_rank) {
+  const int per_row = hidden / 8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < (size_t)tokens * per_row;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int t = i / per_row, c = (i % per_row) * 8;
+    const long long id = ids[t];
+    if (id < vocab_start || id >= vocab_end) continue;  // another rank owns this row and writes it
+    const uint4 v = *reinterpret_cast<const uint4*>(W + (size_t)(id - vocab_start) * hidden + c);
+    if (seq_per_rank > 0) {
+      const int b = t / seq, pos = t % seq;
+      const size_t row = (size_t)b * seq_per_rank + pos % seq_per_rank;
+      *reinterpret_cast<uint4*>(outs.p[pos / seq_per_rank] + row * hidden + c) = v;
+    } else {
+      for (int r = 0; r < outs.n; ++r) *reinterpret_cast<uint4*>(outs.p[r] + (size_t)t * hidden + c) = v;
+    }
+  }
+}
 template <typename G>
 __global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ dout,
                                      G* __restrict__ dW, int tokens, int hidden, long long vocab_start,
@@ -380,6 +408,24 @@ extern "C" int sb_embedding_fwd(const long long* ids, const void* W, void* out, 
   embedding_fwd_kernel<<<blocks_for((size_t)tokens * hidden / 8), 256, 0, st>>>(ids, (const __nv_bfloat16*)W,
                                                                               (__nv_bfloat16*)out, tokens, hidden,
                                                                               vocab_start, vocab_end);
+  return (int)cudaGetLastError();
+}
+// out_ptrs: the tp peer-mapped addresses of the (symmetric) output buffer, rank order, own included.  seq == 0: every
+// rank receives all `tokens` rows; seq > 0: tokens are [batch, seq] and rank r receives positions
+// [r * seq / tp, (r + 1) * seq / tp) of every batch item ([batch * seq / tp, hidden] compact).  The caller brackets the
+// launch with a group barrier (rows arrive from the peers' launches).  Reference: masked F.embedding then all_reduce /
+// reduce_scatter of the dense [b, s, h] tensor (core/nn/linear/vocab_parallel_embedding.py:122-140).
+extern "C" int sb_embedding_fwd_peers(const long long* ids, const void* W, const unsigned long long* out_ptrs, int tp,
+                                      int tokens, int hidden, long long vocab_start, long long vocab_end, int seq,
+                                      cudaStream_t st) {
+  if (tokens <= 0) return 0;
+  if (hidden % 8 || tp < 1 || tp > 8) return -1;
+  if (seq > 0 && (tokens % seq || seq % tp)) return -3;
+  EmbPeers o{};
+  o.n = tp;
+  for (int r = 0; r < tp; ++r) o.p[r] = reinterpret_cast<__nv_bfloat16*>(out_ptrs[r]);
+  embedding_fwd_peers_kernel<<<blocks_for((size_t)tokens * hidden / 8), 256, 0, st>>>(
+      ids, (const __nv_bfloat16*)W, o, tokens, hidden, vocab_start, vocab_end, seq, seq > 0 ? seq / tp : 0);
   return (int)cudaGetLastError();
 }
 extern "C" int sb_embedding_bwd(const long long* ids, const void* dout, void* dW, int grad_fp32, int tokens, int hidden,

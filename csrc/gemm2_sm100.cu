@@ -58,6 +58,7 @@ struct Params {
   int ldaux;
   int swiglu_up_row_offset;
   int tiles_m, tiles_n;
+  int kb_extra;  // k-blocks of the low-rank slab behind the main K range (0 = none)
   // split-K tail: the last, partial wave of tiles is cut along K into `split` parts so that it fills the machine
   int full_tiles;   // tiles [0, full_tiles) run whole; the remaining `num_tiles - full_tiles` are split
   int split;        // parts per tail tile (1 = no splitting)
@@ -280,7 +281,8 @@ SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, int tail_tile, i
 
 template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kEpi == kAllReduce ? kArThreads : kThreads, 1)
-gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
+gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+             const __grid_constant__ CUtensorMap tma_a2, const __grid_constant__ CUtensorMap tma_b2, const Params p) {
   constexpr int kNumStages = kEpi == kAllReduce ? kArStages : kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -291,7 +293,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
   const int num_tiles = p.tiles_m * p.tiles_n;
-  const int k_blocks = (p.K + BK - 1) / BK;
+  // k-blocks [0, kb_main) stream the main operands, [kb_main, k_blocks) the optional low-rank slab (A2 [M, K2] K-major,
+  // B2 in the layout of B): D = A·Bᵀ + A2·B2ᵀ in one accumulator — LoRA as extra K
+  const int kb_main = (p.K + BK - 1) / BK;
+  const int k_blocks = kb_main + p.kb_extra;
   const int num_units = p.full_tiles + (num_tiles - p.full_tiles) * p.split;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
@@ -299,6 +304,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    if (p.kb_extra > 0) {
+      tma_prefetch_desc(&tma_a2);
+      tma_prefetch_desc(&tma_b2);
+    }
     if (kEpi == kAllReduce) prof_stamp(p.prof, 0);
   }
   if (warp == 1 && lane == 0) {
@@ -335,18 +344,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           uint8_t* sa = smem + stage * kStageBytes;
           uint8_t* sb_ = sa + kABytes;
           if (leader) mbar_arrive_expect_tx(&bars->full[stage], 2 * kStageBytes);  // both CTAs' bytes land here
-          const int k0 = kb * BK;
+          const bool extra = kb >= kb_main;
+          const CUtensorMap* ma = extra ? &tma_a2 : &tma_a;
+          const CUtensorMap* mb = extra ? &tma_b2 : &tma_b;
+          const int k0 = (extra ? kb - kb_main : kb) * BK;
           if (kAMajorMN) {
-            tma_load_2d_2sm(sa, &tma_a, &bars->full[stage], m0, k0);
-            tma_load_2d_2sm(sa + 8192, &tma_a, &bars->full[stage], m0 + 64, k0);
+            tma_load_2d_2sm(sa, ma, &bars->full[stage], m0, k0);
+            tma_load_2d_2sm(sa + 8192, ma, &bars->full[stage], m0 + 64, k0);
           } else {
-            tma_load_2d_2sm(sa, &tma_a, &bars->full[stage], k0, m0);
+            tma_load_2d_2sm(sa, ma, &bars->full[stage], k0, m0);
           }
           if (kBMajorMN) {
-            tma_load_2d_2sm(sb_, &tma_b, &bars->full[stage], nb, k0);
-            tma_load_2d_2sm(sb_ + 8192, &tma_b, &bars->full[stage], nb + 64, k0);
+            tma_load_2d_2sm(sb_, mb, &bars->full[stage], nb, k0);
+            tma_load_2d_2sm(sb_ + 8192, mb, &bars->full[stage], nb + 64, k0);
           } else {
-            tma_load_2d_2sm(sb_, &tma_b, &bars->full[stage], k0, nb);
+            tma_load_2d_2sm(sb_, mb, &bars->full[stage], k0, nb);
           }
           if (++stage == kNumStages) {
             stage = 0;
@@ -790,8 +802,45 @@ static bool split_enabled() {
   return on == 1;
 }
 
+// Tensor maps of one launch: main operands plus the optional low-rank slab (copies of the main maps when there is none).
+struct Maps {
+  CUtensorMap a, b, a2, b2;
+};
+struct LowRank {
+  const void* A2;  // [M, K2] row-major (K-major)
+  const void* B2;  // [N, K2] row-major when b_layout == 0, [K2, N] when b_layout == 1
+  int K2, lda2, ldb2;
+};
+static int make_maps(Maps& m, const void* A, const void* B, int M, int N, int K, int lda, int ldb, int a_layout,
+                     int b_layout, const LowRank* lr, Params& p) {
+  int rc;
+  if (a_layout == 0)
+    rc = make_map_2d(&m.a, A, K, M, lda, BK, 128);
+  else
+    rc = make_map_2d(&m.a, A, M, K, lda, 64, BK);
+  if (rc) return 1000 + rc;
+  if (b_layout == 0)
+    rc = make_map_2d(&m.b, B, K, N, ldb, BK, 128);
+  else
+    rc = make_map_2d(&m.b, B, N, K, ldb, 64, BK);
+  if (rc) return 2000 + rc;
+  m.a2 = m.a, m.b2 = m.b;
+  p.kb_extra = 0;
+  if (lr && lr->K2 > 0) {
+    if (a_layout != 0) return -11;  // the slab's A operand is K-major like the main one
+    if (make_map_2d(&m.a2, lr->A2, lr->K2, M, lr->lda2, BK, 128)) return 3000;
+    if (b_layout == 0)
+      rc = make_map_2d(&m.b2, lr->B2, lr->K2, N, lr->ldb2, BK, 128);
+    else
+      rc = make_map_2d(&m.b2, lr->B2, N, lr->K2, lr->ldb2, 64, BK);
+    if (rc) return 4000 + rc;
+    p.kb_extra = (lr->K2 + BK - 1) / BK;
+  }
+  return 0;
+}
+
 template <int AM, int BMj, int EPI, typename OutT>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaStream_t stream, int max_ctas) {
+static int launch(const Maps& m, Params& p, cudaStream_t stream, int max_ctas) {
   auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
   static PerDeviceOnce once;  // the attribute is per device
   if (once.first())
@@ -806,7 +855,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaS
   // workspace and the last one to arrive runs the epilogue on the sum.
   if (EPI != kAllReduce && split_enabled()) {
     const int rem = tiles % width;
-    const int k_blocks = (p.K + BK - 1) / BK;
+    const int k_blocks = (p.K + BK - 1) / BK + p.kb_extra;
     int parts = rem > 0 ? width / rem : 1;
     // Measured on B200 (profiles/kbench_r1_splitk.json): parking and re-reading the 128 KiB partials costs 10-25 us per
     // tail, and the un-split tail already runs at boosted clocks (half the SMs idle under the power cap), so splitting
@@ -823,9 +872,9 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, Params& p, cudaS
   const int units = p.full_tiles + (tiles - p.full_tiles) * p.split;
   const int clusters = units < width ? units : width;
   if (EPI == kAllReduce)
-    kern<<<clusters * 2, kArThreads, kArSmemBytes, stream>>>(ta, tb, p);
+    kern<<<clusters * 2, kArThreads, kArSmemBytes, stream>>>(m.a, m.b, m.a2, m.b2, p);
   else
-    kern<<<clusters * 2, kThreads, kSmemBytes, stream>>>(ta, tb, p);
+    kern<<<clusters * 2, kThreads, kSmemBytes, stream>>>(m.a, m.b, m.a2, m.b2, p);
   return (int)cudaGetLastError();
 }
 
@@ -852,33 +901,22 @@ extern "C" int sb_gemm2_set_split_workspace(void* base, unsigned long long bytes
   return 0;
 }
 
-// Same contract as sb_gemm_bf16 (gemm_sm100.cu), computed by CTA pairs (cta_group::2).
-extern "C" int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
-                             int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas,
-                             cudaStream_t stream) {
+static int gemm2_impl(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
+                      int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, const LowRank* lr, int max_ctas,
+                      cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
-  CUtensorMap ta, tb;
-  int rc;
-  if (a_layout == 0)
-    rc = make_map_2d(&ta, A, K, M, lda, BK, 128);
-  else
-    rc = make_map_2d(&ta, A, M, K, lda, 64, BK);
-  if (rc) return 1000 + rc;
-  if (b_layout == 0)
-    rc = make_map_2d(&tb, B, K, N, ldb, BK, 128);
-  else
-    rc = make_map_2d(&tb, B, N, K, ldb, 64, BK);
-  if (rc) return 2000 + rc;
   Params p{};
+  Maps m;
+  if (int rc = make_maps(m, A, B, M, N, K, lda, ldb, a_layout, b_layout, lr, p)) return rc;
   p.M = M, p.N = N, p.K = K, p.D = D, p.ldd = ldd, p.bias = bias;
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + BN - 1) / BN;
-#define SB_DISPATCH(AM, BMj)                                                                                          \
-  if (a_layout == AM && b_layout == BMj) {                                                                            \
-    if (epilogue == 0 && out_dtype == 0) return launch<AM, BMj, kStore, __nv_bfloat16>(ta, tb, p, stream, max_ctas);      \
-    if (epilogue == 0 && out_dtype == 1) return launch<AM, BMj, kStore, float>(ta, tb, p, stream, max_ctas);              \
-    if (epilogue == 1 && out_dtype == 0) return launch<AM, BMj, kAccumulate, __nv_bfloat16>(ta, tb, p, stream, max_ctas); \
-    if (epilogue == 1 && out_dtype == 1) return launch<AM, BMj, kAccumulate, float>(ta, tb, p, stream, max_ctas);         \
+#define SB_DISPATCH(AM, BMj)                                                                                  \
+  if (a_layout == AM && b_layout == BMj) {                                                                    \
+    if (epilogue == 0 && out_dtype == 0) return launch<AM, BMj, kStore, __nv_bfloat16>(m, p, stream, max_ctas);      \
+    if (epilogue == 0 && out_dtype == 1) return launch<AM, BMj, kStore, float>(m, p, stream, max_ctas);              \
+    if (epilogue == 1 && out_dtype == 0) return launch<AM, BMj, kAccumulate, __nv_bfloat16>(m, p, stream, max_ctas); \
+    if (epilogue == 1 && out_dtype == 1) return launch<AM, BMj, kAccumulate, float>(m, p, stream, max_ctas);         \
   }
   SB_DISPATCH(0, 0)
   SB_DISPATCH(0, 1)
@@ -888,18 +926,39 @@ extern "C" int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* 
   return -10;
 }
 
+// Same contract as sb_gemm_bf16 (gemm_sm100.cu), computed by CTA pairs (cta_group::2).
+extern "C" int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
+                             int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas,
+                             cudaStream_t stream) {
+  return gemm2_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, a_layout, b_layout, out_dtype, epilogue, nullptr, max_ctas,
+                    stream);
+}
+
+// LoRA-fused linear: D[M,N] (+)= A·Bᵀ + A2·B2ᵀ in ONE accumulator — the low-rank pair rides as extra
+// k-blocks behind the main K range, so Y = X·Wᵀ + (s·X·Aᵀ)·B_loraᵀ costs one launch and no extra pass over Y.
+// A [M,K] and A2 [M,K2] are row-major; B/B2 are [N,K]/[N,K2] (b_layout 0) or [K,N]/[K2,N] (b_layout 1); K2 % 8 == 0.
+// Reference: separate F.linear calls and an add (core/nn/lora.py:103-112, core/nn/attention/attention.py:709-744).
+extern "C" int sb_gemm2_lowrank_bf16(const void* A, const void* B, const void* A2, const void* B2, void* D,
+                                     const void* bias, int M, int N, int K, int K2, int lda, int ldb, int lda2, int ldb2,
+                                     int ldd, int b_layout, int out_dtype, int epilogue, int max_ctas,
+                                     cudaStream_t stream) {
+  LowRank lr{A2, B2, K2, lda2, ldb2};
+  return gemm2_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, 0, b_layout, out_dtype, epilogue, &lr, max_ctas, stream);
+}
+
 // Same contract as sb_gemm_swiglu_bf16: CTA 0 of the pair stages the gate rows, CTA 1 the up rows of the tile.
 extern "C" int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
                                     int ldh, int ldpre, int max_ctas, cudaStream_t stream) {
   if (M <= 0 || F <= 0 || K <= 0) return 0;
-  CUtensorMap ta, tb;
-  if (int rc = make_map_2d(&ta, X, K, M, ldx, BK, 128)) return 1000 + rc;
-  if (int rc = make_map_2d(&tb, W, K, 2 * (uint64_t)F, ldw, BK, 128)) return 2000 + rc;
+  Maps m;
+  if (int rc = make_map_2d(&m.a, X, K, M, ldx, BK, 128)) return 1000 + rc;
+  if (int rc = make_map_2d(&m.b, W, K, 2 * (uint64_t)F, ldw, BK, 128)) return 2000 + rc;
+  m.a2 = m.a, m.b2 = m.b;
   Params p{};
   p.M = M, p.N = F, p.K = K, p.D = H, p.ldd = ldh, p.aux = pre, p.ldaux = ldpre, p.swiglu_up_row_offset = F;
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (F + BN / 2 - 1) / (BN / 2);
-  return launch<0, 0, kSwiGLU, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
+  return launch<0, 0, kSwiGLU, __nv_bfloat16>(m, p, stream, max_ctas);
 }
 
 // Optional phase profile of the fused collective kernels: a caller-owned buffer of grid x 8 u64 (148 x 8 is enough) for
@@ -921,22 +980,12 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
                                  int ldb, int ldd, int a_layout, int b_layout, const unsigned long long* data_ptrs,
                                  const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
                                  unsigned long long slot_bytes, unsigned int flag_slot, int rs_seq, int max_ctas,
-                                 cudaStream_t stream) {
+                                 cudaStream_t stream, const LowRank* lr = nullptr) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if (tp_size < 2 || tp_size > kMaxTP || tp_rank < 0 || tp_rank >= tp_size) return -20;
-  CUtensorMap ta, tb;
-  int rc;
-  if (a_layout == 0)
-    rc = make_map_2d(&ta, A, K, M, lda, BK, 128);
-  else
-    rc = make_map_2d(&ta, A, M, K, lda, 64, BK);
-  if (rc) return 1000 + rc;
-  if (b_layout == 0)
-    rc = make_map_2d(&tb, B, K, N, ldb, BK, 128);
-  else
-    rc = make_map_2d(&tb, B, N, K, ldb, 64, BK);
-  if (rc) return 2000 + rc;
   Params p{};
+  Maps m;
+  if (int rc = make_maps(m, A, B, M, N, K, lda, ldb, a_layout, b_layout, lr, p)) return rc;
   p.M = M, p.N = N, p.K = K, p.D = D, p.ldd = ldd, p.bias = bias;
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + BN - 1) / BN;
@@ -953,8 +1002,8 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
     p.ar_data[r] = reinterpret_cast<uint8_t*>(data_ptrs[r]);
     p.ar_flags[r] = reinterpret_cast<uint32_t*>(flag_ptrs[r]);
   }
-  if (a_layout == 0 && b_layout == 0) return launch<0, 0, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
-  if (a_layout == 0 && b_layout == 1) return launch<0, 1, kAllReduce, __nv_bfloat16>(ta, tb, p, stream, max_ctas);
+  if (a_layout == 0 && b_layout == 0) return launch<0, 0, kAllReduce, __nv_bfloat16>(m, p, stream, max_ctas);
+  if (a_layout == 0 && b_layout == 1) return launch<0, 1, kAllReduce, __nv_bfloat16>(m, p, stream, max_ctas);
   return -10;
 }
 
@@ -979,6 +1028,18 @@ extern "C" int sb_gemm2_allreduce_bf16(const void* A, const void* B, void* D, co
                                        cudaStream_t stream) {
   return fused_collective_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, a_layout, b_layout, data_ptrs, flag_ptrs, tp_rank,
                                tp_size, epoch, slot_bytes, flag_slot, 0, max_ctas, stream);
+}
+
+// Fused all-reduce with a low-rank slab (see sb_gemm2_lowrank_bf16): D = Σ_ranks (A·Bᵀ + A2·B2ᵀ) (+ bias).
+extern "C" int sb_gemm2_allreduce_lowrank_bf16(const void* A, const void* B, const void* A2, const void* B2, void* D,
+                                               const void* bias, int M, int N, int K, int K2, int lda, int ldb, int lda2,
+                                               int ldb2, int ldd, int b_layout, const unsigned long long* data_ptrs,
+                                               const unsigned long long* flag_ptrs, int tp_rank, int tp_size,
+                                               unsigned int epoch, unsigned long long slot_bytes, unsigned int flag_slot,
+                                               int max_ctas, cudaStream_t stream) {
+  LowRank lr{A2, B2, K2, lda2, ldb2};
+  return fused_collective_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, 0, b_layout, data_ptrs, flag_ptrs, tp_rank,
+                               tp_size, epoch, slot_bytes, flag_slot, 0, max_ctas, stream, &lr);
 }
 
 // Bytes of workspace one sender slot needs for an [M, N] fused all-reduce, and flags per slot.

@@ -199,6 +199,33 @@ __global__ void __launch_bounds__(kThreads) peer_reduce_kernel(InPtrs<G> ins, G*
   }
 }
 
+// Fused data-parallel all-reduce (no ZeRO): this rank owns one 1/dp chunk of the gradient arena; it reads that chunk from
+// every peer's arena (NVLink loads), sums in rank order and stores the sum back into every peer's arena (NVLink stores)
+// — reduce-scatter and all-gather in one pass, no intermediate buffer.  Chunks of different ranks are disjoint, so no
+// rank ever writes what another rank is still reading; barriers before and after the launch bracket it.
+template <typename G>
+__global__ void __launch_bounds__(kThreads) peer_allreduce_kernel(OutPtrs<G> io, size_t n) {
+  const size_t n4 = n / 4;
+  for (size_t i = blockIdx.x * (size_t)kThreads + threadIdx.x; i < n4; i += (size_t)gridDim.x * kThreads) {
+    const size_t e = i * 4;
+    float acc[4], x[4];
+    V4<G>::load(io.p[0] + e, acc);
+    for (int r = 1; r < io.n; ++r) {
+      V4<G>::load(io.p[r] + e, x);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc[k] += x[k];
+    }
+    for (int r = 0; r < io.n; ++r) V4<G>::store(io.p[r] + e, acc);
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = n4 * 4 + threadIdx.x; i < n; i += kThreads) {
+      float acc = (float)io.p[0][i];
+      for (int r = 1; r < io.n; ++r) acc += (float)io.p[r][i];
+      for (int r = 0; r < io.n; ++r) io.p[r][i] = (G)acc;
+    }
+  }
+}
+
 // dst (P) <- src (fp32) cast, used when refreshing the model copy from master weights
 template <typename P>
 __global__ void cast_kernel(const float* __restrict__ src, P* __restrict__ dst, size_t n) {
@@ -312,6 +339,30 @@ extern "C" int sb_zero_reduce(const unsigned long long* peer_grads, int n_peers,
     in.n = n_peers;
     for (int r = 0; r < n_peers; ++r) in.p[r] = (const __nv_bfloat16*)peer_grads[r];
     peer_reduce_kernel<__nv_bfloat16><<<b, kThreads, 0, st>>>(in, (__nv_bfloat16*)own, (size_t)n);
+  } else {
+    return -2;
+  }
+  return (int)cudaGetLastError();
+}
+
+// Data-parallel gradient all-reduce without ZeRO: `peer_chunks` are the dp peer-mapped addresses of THIS
+// rank's chunk inside every rank's gradient arena, in rank order (own included); every address receives the sum.
+// Reference: flatten -> fp32 copy -> NCCL all_reduce -> copy back (core/optimizer/allreduce.py:16-22).
+extern "C" int sb_dp_allreduce(const unsigned long long* peer_chunks, int n_peers, long long n, int grad_dtype,
+                               cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n_peers < 1 || n_peers > kMaxPeers) return -5;
+  const int b = blocks((size_t)n / 4 + 1);
+  if (grad_dtype == 1) {
+    OutPtrs<float> io{};
+    io.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) io.p[r] = (float*)peer_chunks[r];
+    peer_allreduce_kernel<float><<<b, kThreads, 0, st>>>(io, (size_t)n);
+  } else if (grad_dtype == 0) {
+    OutPtrs<__nv_bfloat16> io{};
+    io.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) io.p[r] = (__nv_bfloat16*)peer_chunks[r];
+    peer_allreduce_kernel<__nv_bfloat16><<<b, kThreads, 0, st>>>(io, (size_t)n);
   } else {
     return -2;
   }

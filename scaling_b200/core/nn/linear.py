@@ -165,6 +165,13 @@ class VocabParallelEmbedding(torch.nn.Module):
         return self._grad_mask
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        sp = self.topology is not None and bool(self.topology.config.sequence_parallel)
+        if self.model_parallel_size > 1 and self.weight.is_cuda:
+            # every row lives on one rank: its owner stores it into the peers' outputs over NVLink (no dense all-reduce)
+            out = OF.vocab_embedding_reduced(x, self.weight, self.vocab_start_index, self.vocab_end_index,
+                                             get_tp_comm(self.topology, sequence_parallel=sp), sp)
+            if out is not None:
+                return out
         out = OF.vocab_embedding(x, self.weight, self.vocab_start_index, self.vocab_end_index)
         if self.topology is not None and self.topology.config.sequence_parallel:
             return all_reduce_scatter_to_sequence_parallel(out, self.topology)

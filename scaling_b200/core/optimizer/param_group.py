@@ -109,23 +109,24 @@ class OptimizerParamGroup:
         self.used = off
         self.counted_end = off if counted_end is None else counted_end
         dp = topology.config.data_parallel_size if self.zero else 1
-        self.total = _round_up(max(off, ALIGN), ALIGN * dp)
+        dp_all = topology.config.data_parallel_size
+        self.total = _round_up(max(off, ALIGN), ALIGN * dp_all)  # divisible into dp chunks with or without ZeRO
         self._sym_params = self._sym_grads = None
-        if self.zero:
+        if dp_all > 1:
             from ...parallel.symm import SymmetricArena, fused_zero_enabled
 
             if fused_zero_enabled(topology) and self.grad_dtype in native.DTYPE_CODE and self.model_dtype in native.DTYPE_CODE:
-                # arenas every DP rank can address: the reduce-scatter becomes peer loads inside the reduce kernel and
-                # the all-gather peer stores inside the AdamW kernel (collective: all DP ranks build their groups in
-                # the same order)
-                self._sym_params = SymmetricArena(self.total, self.model_dtype, topology.data_parallel_group, device)
+                # arenas every DP rank can address (collective: all DP ranks build their groups in the same order).
+                # ZeRO: the reduce-scatter becomes peer loads inside the reduce kernel and the all-gather peer stores
+                # inside the AdamW kernel.  Plain DP: one kernel reads this rank's chunk from every peer and stores the
+                # sum back into every peer (sb_dp_allreduce) — only the gradient arena has to be shared.
+                if self.zero:
+                    self._sym_params = SymmetricArena(self.total, self.model_dtype, topology.data_parallel_group, device)
                 self._sym_grads = SymmetricArena(self.total, self.grad_dtype, topology.data_parallel_group, device)
-        if self._sym_params is not None:
-            self.param_arena = self._sym_params.tensor
-            self.grad_arena = self._sym_grads.tensor
-        else:
-            self.param_arena = torch.zeros(self.total, dtype=self.model_dtype, device=device)
-            self.grad_arena = torch.zeros(self.total, dtype=self.grad_dtype, device=device)
+        self.param_arena = self._sym_params.tensor if self._sym_params is not None else \
+            torch.zeros(self.total, dtype=self.model_dtype, device=device)
+        self.grad_arena = self._sym_grads.tensor if self._sym_grads is not None else \
+            torch.zeros(self.total, dtype=self.grad_dtype, device=device)
         for p, o in zip(self.parameters_original, self.offsets):
             n = p.numel()
             view = self.param_arena[o:o + n].view(p.shape)
@@ -186,11 +187,19 @@ class OptimizerParamGroup:
         topo = self.topology
         if topo.config.data_parallel_size == 1 or not topo.is_distributed_initialized:
             return
-        if self._sym_grads is not None:
+        if self._sym_grads is not None and self.zero:
             n = self.shard_end - self.shard_start
             self._sym_grads.barrier()  # every rank's backward (its writes to its own arena) is complete
             native.call("sb_zero_reduce", self._sym_grads.ptr_array(self.shard_start), self._sym_grads.world,
                         native.ptr(self.grad_shard), n, native.DTYPE_CODE[self.grad_dtype])
+        elif self._sym_grads is not None:
+            # plain DP: this rank sums chunk `dp_rank` of every arena and stores it into every arena
+            dp = topo.config.data_parallel_size
+            n = self.total // dp
+            self._sym_grads.barrier()
+            native.call("sb_dp_allreduce", self._sym_grads.ptr_array(topo.data_parallel_rank * n), dp, n,
+                        native.DTYPE_CODE[self.grad_dtype])
+            self._sym_grads.barrier()  # every chunk of this rank's arena has been written by its owner
         elif self.zero and topo.backend == "nccl":
             dist.reduce_scatter_tensor(self.grad_shard, self.grad_arena, group=topo.data_parallel_group)
         else:

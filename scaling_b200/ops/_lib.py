@@ -42,6 +42,7 @@ _SIGS = {
     "sb_dropout_bwd": [P, P, c_longlong, c_float, c_ulonglong, c_ulonglong, P],
     "sb_embedding_fwd": [P, P, P, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
+    "sb_embedding_fwd_peers": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_xent_stats": [P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_xent_grad": [P, P, P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_attention_fwd": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float, c_int, P],
@@ -54,6 +55,8 @@ _SIGS = {
     "sb_adamw_zero": [P, P, P, P, P, c_int, c_longlong, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_int,
                       c_float, c_float, P, P, c_int, P],
     "sb_zero_reduce": [P, c_int, P, c_longlong, c_int, P],
+    "sb_dp_allreduce": [P, c_int, c_longlong, c_int, P],
+    "sb_device_barrier": [P, c_int, c_int, c_uint, P],
 }
 _RET_LL = {
     "sb_norm_bwd_scratch_floats": [c_int, c_int, c_int],

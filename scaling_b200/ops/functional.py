@@ -9,7 +9,7 @@ weight gradient — no per-micro-batch ``.grad`` tensors, no separate accumulati
 from __future__ import annotations
 
 import os
-from typing import Optional, Tuple
+from typing import Any, Optional, Tuple
 
 import torch
 import torch.nn.functional as F
@@ -557,6 +557,61 @@ class _EmbeddingFn(torch.autograd.Function):
         dw = torch.zeros(w.shape, dtype=torch.float32, device=w.device)
         K.embedding_bwd(ids, dout.contiguous(), dw, *ctx.range)
         return None, dw.to(w.dtype), None, None
+
+
+class _EmbeddingPeersFn(torch.autograd.Function):
+    """Vocab-parallel embedding INCLUDING its tensor-parallel reduction, done by placement instead of arithmetic: the
+    rank that owns a token's row stores it into every rank's output (or, under sequence parallelism, into the output of
+    the rank that owns the token's sequence position) with NVLink peer stores — ``sb_embedding_fwd_peers`` — followed
+    by one device barrier.  Replaces masked lookup + dense all-reduce / reduce-scatter of [b, s, h]
+    (reference core/nn/linear/vocab_parallel_embedding.py:122-140)."""
+
+    @staticmethod
+    def forward(ctx, ids, weight, vocab_start, vocab_end, comm, sp_group_size):
+        ids = ids.contiguous()
+        b, s = (ids.shape[0], ids.shape[1]) if ids.dim() == 2 else (1, ids.numel())
+        hidden = weight.shape[1]
+        rows = ids.numel() // sp_group_size if sp_group_size else ids.numel()
+        staging, ptrs = comm.exchange_buffer("embedding", rows * hidden * 2)
+        _lib.call("sb_embedding_fwd_peers", _lib.ptr(ids), _lib.ptr(weight), ptrs, comm.size, ids.numel(), hidden,
+                     vocab_start, vocab_end, s if sp_group_size else 0)
+        comm.barrier()  # the peers' rows have landed here
+        out_shape = (*ids.shape[:-1], ids.shape[-1] // sp_group_size if sp_group_size else ids.shape[-1], hidden)
+        out = staging.view(torch.bfloat16).view(out_shape).clone()  # leave the exchange buffer to the next call
+        ctx.save_for_backward(ids)
+        ctx.weight_ref = weight
+        ctx.range = (vocab_start, vocab_end)
+        ctx.sp = (comm.size, comm.group) if sp_group_size else None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        w = ctx.weight_ref
+        dout = dout.contiguous()
+        if ctx.sp is not None:  # gradient of the scatter along the sequence: gather it back (dim 1)
+            size, group = ctx.sp
+            parts = torch.empty((size, *dout.shape), dtype=dout.dtype, device=dout.device)
+            torch.distributed.all_gather_into_tensor(parts, dout, group=group)
+            dout = torch.cat(list(parts.unbind(0)), dim=-2).contiguous()
+        main = getattr(w, "main_grad", None)
+        if main is not None:
+            K.embedding_bwd(ids, dout, main, *ctx.range)
+            return None, None, None, None, None, None
+        dw = torch.zeros(w.shape, dtype=torch.float32, device=w.device)
+        K.embedding_bwd(ids, dout, dw, *ctx.range)
+        return None, dw.to(w.dtype), None, None, None, None
+
+
+def vocab_embedding_reduced(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int, comm: Any,
+                            sequence_parallel: bool) -> Optional[torch.Tensor]:
+    """The embedding already summed over the TP group (replicated, or scattered along the sequence when
+    ``sequence_parallel``) through peer stores, or None when that path does not apply (the caller then reduces)."""
+    if comm is None or not native_enabled(weight) or weight.dtype != torch.bfloat16 or weight.shape[1] % 8 or ids.numel() == 0:
+        return None
+    if sequence_parallel and (ids.dim() != 2 or ids.shape[1] % comm.size):
+        return None
+    return _EmbeddingPeersFn.apply(ids.long(), weight, vocab_start, vocab_end, comm, comm.size if sequence_parallel else 0)
 
 
 def vocab_embedding(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int) -> torch.Tensor:

@@ -57,6 +57,8 @@ class TPComm:
         self._hdl: Any = None
         self._data_ptrs = [None, None]
         self._flag_ptrs = [None, None]
+        self._xbufs: Dict[str, Any] = {}
+        self._barrier: Optional["GroupBarrier"] = None
 
     # ---- workspace -------------------------------------------------------------------------------------------
     def _allocate(self, slot_bytes: int) -> None:
@@ -103,6 +105,36 @@ class TPComm:
         parity = self.calls & 1
         return self.calls, self._data_ptrs[parity], self._flag_ptrs[parity]
 
+    # ---- exchange buffers (embedding rows, sequence-parallel gathers) ---------------------------------------------
+    def exchange_buffer(self, tag: str, nbytes: int):
+        """(local tensor, peer pointer array) of a double-buffered symmetric byte buffer named ``tag``: peers store into
+        it with plain NVLink stores, a :meth:`barrier` publishes them.  Successive calls alternate between two halves,
+        so a rank that is one call ahead never overwrites data a slower peer is still reading (it cannot get two calls
+        ahead: every call contains a barrier).  Collective when it has to (re)allocate."""
+        import torch.distributed._symmetric_memory as symm_mem
+
+        ent = self._xbufs.get(tag)
+        if ent is None or ent["bytes"] < nbytes:
+            torch.cuda.synchronize(self.device)
+            cap = (max(nbytes, 1 << 20) + 65535) // 65536 * 65536
+            buf = symm_mem.empty(2 * cap, dtype=torch.uint8, device=self.device)
+            hdl = symm_mem.rendezvous(buf, self.group.group_name)
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+            ent = self._xbufs[tag] = {"bytes": cap, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs],
+                                      "calls": 0}
+        ent["calls"] += 1
+        half = ent["calls"] & 1
+        off = half * ent["bytes"]
+        arr = ctypes.c_ulonglong * self.size
+        return ent["buf"][off:off + nbytes], arr(*[p + off for p in ent["ptrs"]])
+
+    def barrier(self) -> None:
+        """Device-side barrier over the TP group on the current stream (own kernel)."""
+        if self._barrier is None:
+            self._barrier = GroupBarrier.get(self.group, self.device)
+        self._barrier()
+
     # ---- torch.distributed expressions of the same collectives (guards / oracle) ---------------------------------
     def all_reduce_(self, x: torch.Tensor) -> torch.Tensor:
         dist.all_reduce(x, group=self.group)
@@ -118,12 +150,50 @@ def set_fused_zero(enabled: bool) -> None:
 
 
 def fused_zero_enabled(topology: Any) -> bool:
-    """ZeRO-1 reduce-scatter / all-gather as peer loads / stores inside the optimizer kernels: NCCL job on CUDA, 2..8
+    """Data-parallel gradient reduction as peer loads / stores inside this library's kernels (ZeRO-1: reduce-scatter in
+    ``sb_zero_reduce`` + all-gather in ``sb_adamw_zero``; plain DP: ``sb_dp_allreduce``): NCCL job on CUDA, 2..8
     data-parallel ranks (one NVLink domain), native library present."""
     if topology is None or not _FUSED_ZERO or not topology.is_distributed_initialized:
         return False
     dp = topology.config.data_parallel_size
     return (2 <= dp <= 8 and topology.backend == "nccl" and topology.device.type == "cuda" and _lib.available())
+
+
+class GroupBarrier:
+    """Device-side barrier of one process group: this library's own kernel (``sb_device_barrier``, csrc/runtime.cu) over
+    a few flag words in symmetric memory — one launch on the current stream, no host synchronisation, no NCCL."""
+
+    _by_group: Dict[str, "GroupBarrier"] = {}
+
+    def __init__(self, group: Any, device: torch.device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        name = group.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(name)
+        except Exception:  # noqa: BLE001
+            pass
+        self._flags = symm_mem.empty(64, dtype=torch.int32, device=device)
+        self._hdl = symm_mem.rendezvous(self._flags, name)
+        self._flags.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)  # every rank's flags are zero before anybody may post epoch 1
+        self.rank, self.world = self._hdl.rank, self._hdl.world_size
+        arr = ctypes.c_ulonglong * self.world
+        self._ptrs = arr(*[int(p) for p in self._hdl.buffer_ptrs])
+        self.epoch = 0
+
+    @classmethod
+    def get(cls, group: Any, device: torch.device) -> "GroupBarrier":
+        key = f"{group.group_name}@{device.index}"
+        b = cls._by_group.get(key)
+        if b is None:
+            b = cls._by_group[key] = GroupBarrier(group, device)
+        return b
+
+    def __call__(self) -> None:
+        self.epoch = (self.epoch + 1) & 0xFFFFFFFF
+        _lib.call("sb_device_barrier", self._ptrs, self.rank, self.world, self.epoch)
 
 
 class SymmetricArena:
@@ -146,10 +216,11 @@ class SymmetricArena:
         self.rank = self._hdl.rank
         self.world = self._hdl.world_size
         self.itemsize = self._buf.element_size()
+        self._barrier = GroupBarrier.get(group, device)
 
     def barrier(self) -> None:
-        """Device-side barrier over the group on the current stream."""
-        self._hdl.barrier()
+        """Device-side barrier over the group on the current stream (own kernel, see :class:`GroupBarrier`)."""
+        self._barrier()
 
     def ptr_array(self, element_offset: int):
         arr = ctypes.c_ulonglong * self.world

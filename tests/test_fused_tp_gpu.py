@@ -236,6 +236,72 @@ def test_dp2_fused_zero_matches_nccl(tmp_path):
     assert fused[-1][0] < fused[0][0]
 
 
+def test_dp2_fused_allreduce_without_zero_matches_nccl(tmp_path):
+    """Plain data parallelism (optimizer.zero = false): the gradient all-reduce as ONE kernel of peer loads + peer
+    stores (sb_dp_allreduce) against NCCL all_reduce — two summands commute, so the runs agree bitwise."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=512, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 256, "num_attention_heads": 2, "attention_num_kv_heads": 1,
+         "sequence_length": 128, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"}}
+    cfg = tiny_config(prefix, dp=2, iters=6, gas=2, arch=a, optimizer={"zero": False})
+    fused = dist_launcher(_zero_worker, world_size=2, timeout=400, config_dict=cfg, fused=True)[0]
+    plain = dist_launcher(_zero_worker, world_size=2, timeout=400, config_dict=cfg, fused=False)[0]
+    assert len(fused) == 6
+    assert fused == plain, (fused, plain)
+    assert fused[-1][0] < fused[0][0]
+
+
+def _dp_kernel_stress_worker(rank, world_size, master_port):
+    """Device barrier + peer reduce / all-reduce kernels under random per-rank launch skew, many iterations."""
+    import random
+
+    import torch
+    import torch.distributed as dist
+
+    from scaling_b200.ops import _lib as native
+    from scaling_b200.parallel.symm import SymmetricArena
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{master_port}", rank=rank, world_size=world_size,
+                            device_id=torch.device("cuda", rank))
+    dev = torch.device("cuda", rank)
+    n = 3 * 1024 * 128 * world_size + 128 * world_size
+    arena = SymmetricArena(n, torch.float32, dist.group.WORLD, dev)
+    shard = n // world_size
+    own = torch.empty(shard, device=dev)
+    rng = random.Random(1234 + rank)
+    spin = torch.empty(1 << 22, device=dev)
+    ok = True
+    for it in range(60):
+        g = torch.Generator(device="cuda").manual_seed(1000 * it + rank)
+        local = torch.randn(n, device=dev, generator=g)
+        arena.tensor.copy_(local)
+        for _ in range(rng.randrange(0, 4)):  # random skew: this rank reaches the barrier late
+            spin.normal_()
+        expect = torch.zeros(n, device=dev)
+        for r in range(world_size):
+            gr = torch.Generator(device="cuda").manual_seed(1000 * it + r)
+            expect += torch.randn(n, device=dev, generator=gr)
+        arena.barrier()
+        if it % 2 == 0:  # ZeRO flavour: reduce the own shard out of every arena
+            native.call("sb_zero_reduce", arena.ptr_array(rank * shard), world_size, native.ptr(own), shard, 1)
+            arena.barrier()
+            ok = ok and torch.equal(own, expect[rank * shard:(rank + 1) * shard])
+        else:  # plain DP flavour: all-reduce in place
+            native.call("sb_dp_allreduce", arena.ptr_array(rank * shard), world_size, shard, 1)
+            arena.barrier()
+            ok = ok and torch.equal(arena.tensor, expect)
+        arena.barrier()  # nobody overwrites its arena while a peer still reads it
+    torch.cuda.synchronize()
+    dist.barrier()
+    dist.destroy_process_group()
+    return bool(ok)
+
+
+def test_dp_reduce_kernels_and_device_barrier_under_launch_skew():
+    assert all(dist_launcher(_dp_kernel_stress_worker, world_size=2, timeout=300).values())
+
+
 def test_sequence_parallel_fused_reduce_scatter_matches_nccl(tmp_path):
     """Sequence-parallel TP=2 training with the row-parallel reduce-scatters inside the GEMM launch against the same
     run on NCCL reduce-scatters."""
