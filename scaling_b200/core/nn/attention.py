@@ -229,6 +229,41 @@ class ParallelSelfAttention(torch.nn.Module):
             q, k, v = (OF.linear(x, m.weight, bb) for m, bb in zip((self.query, self.key, self.value), biases))
         return q.reshape(T, nh, d), k.reshape(T, nkv, d), v.reshape(T, nkv, d)
 
+    def _lora_fusable(self) -> bool:
+        c = self.lora_config
+        return (c is not None and not self.lora_merged_state and not c.bias and not c.dropout and not self._sp()
+                and not self.qkv_in_one and self.kv_replicas == 1 and OF.lora_fusion_enabled())
+
+    def _tp_triple(self):
+        t = self.topology
+        if t is None or t.config.model_parallel_size == 1:
+            return (1, 0, None)
+        return (t.config.model_parallel_size, t.model_parallel_rank, t.model_parallel_group)
+
+    def _project_qkv_lora(self, x: torch.Tensor):
+        """q/k/v with their LoRA updates inside the projection GEMMs (low-rank K-slab, OF.lora_linear); None when the
+        fused form does not apply (then: plain projections + separate LoRA linears)."""
+        if not self._lora_fusable() or not x.is_cuda or any(
+                m.get_bias() is not None for m in (self.query, self.key, self.value)):
+            return None
+        b, s, _ = x.shape
+        T = b * s
+        nh, nkv, d = self.num_attention_heads_per_partition, self.num_kv_heads_per_partition, self.head_dim
+        comm = get_tp_comm(self.topology)
+        tp = self._tp_triple()
+        outs = []
+        for kind, base, heads in (("query", self.query, nh), ("key", self.key, nkv), ("value", self.value, nkv)):
+            mod = self.lora_modules[f"{kind}_{self.lora_config.name}"] if f"{kind}_{self.lora_config.name}" in self.lora_modules else None
+            y = None
+            if mod is not None:
+                y = OF.lora_linear(x, base.weight, mod.dense_in.weight, mod.dense_out.weight, mod.scaling, "column", tp, comm)
+                if y is None:
+                    return None
+            else:
+                y = base(x)
+            outs.append(y.reshape(T, heads, d))
+        return tuple(outs)
+
     def forward(self, x: torch.Tensor, cumulative_seq_lengths: Optional[torch.Tensor],
                 position_ids: Optional[torch.Tensor], cumulative_seq_lengths_key: Optional[torch.Tensor] = None,
                 use_cache: bool = False, reset_cache: bool = False, cache_index: int = 0,
@@ -241,10 +276,13 @@ class ParallelSelfAttention(torch.nn.Module):
         if fused is not None:
             q, k, v = fused
         else:
-            q, k, v = self._project_qkv(x)
-
-            if self.lora_config is not None and not self.lora_merged_state:
-                q, k, v = self._apply_lora(x, q, k, v)
+            lora_fused = self._project_qkv_lora(x)
+            if lora_fused is not None:
+                q, k, v = lora_fused
+            else:
+                q, k, v = self._project_qkv(x)
+                if self.lora_config is not None and not self.lora_merged_state:
+                    q, k, v = self._apply_lora(x, q, k, v)
 
             if self.key_query_norm:
                 # every TP rank holds a replica of the per-head norm weights; norm over the local heads is identical math
@@ -310,6 +348,17 @@ class ParallelSelfAttention(torch.nn.Module):
             if bias is not None:
                 out = out + bias
         else:
+            dense_lora = self.lora_modules[f"dense_{self.lora_config.name}"] if (
+                self._lora_fusable() and ctx.is_cuda and f"dense_{self.lora_config.name}" in self.lora_modules) else None
+            out = None
+            if dense_lora is not None:
+                # base product and low-rank update are per-rank partial sums of the same all-reduce: one launch, and
+                # the attention output is never gathered (reference attention.py:693 all-gathers [b, s, h] here)
+                out = OF.lora_linear(ctx, self.dense.weight, dense_lora.dense_in.weight, dense_lora.dense_out.weight,
+                                     dense_lora.scaling, "row", self._tp_triple(), get_tp_comm(self.topology))
+                if out is not None:
+                    bias = self.dense.get_bias()
+                    return out if bias is None else out + bias
             out = self.dense(ctx, reduce=True)  # Σ over the ranks' heads (+ bias once), fused into the GEMM launch
         if self.lora_config and not self.lora_merged_state and LoRAModuleType.DENSE in self.lora_config.parallel_modules:
             full = all_concat(ctx, dim=-1, topology=self.topology)

@@ -25,6 +25,10 @@ _SIGS = {
     "sb_gemm_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm2_lowrank_bf16": [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                              c_int, c_int, P],
+    "sb_gemm2_allreduce_lowrank_bf16": [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        c_int, P, P, c_int, c_int, c_uint, c_ulonglong, c_uint, c_int, P],
     "sb_gemm2_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_allreduce_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int,
                                 c_uint, c_ulonglong, c_uint, c_int, P],

@@ -200,6 +200,117 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     return y if bias is None else y + bias
 
 
+# ------------------------------------------------------------------------------------------------ LoRA-fused linear
+def _gather_dim(t: torch.Tensor, dim: int, tp) -> torch.Tensor:
+    size, _, group = tp
+    if size == 1:
+        return t
+    parts = torch.empty((size, *t.shape), dtype=t.dtype, device=t.device)
+    torch.distributed.all_gather_into_tensor(parts, t.contiguous(), group=group)
+    return torch.cat(list(parts.unbind(0)), dim=dim).contiguous()
+
+
+class _LoraLinearFn(torch.autograd.Function):
+    """y = x·Wᵀ + s·(x·Aᵀ)·Bᵀ with the low-rank pair riding as an extra K-slab of the base GEMM, forward AND backward
+    (reference core/nn/lora.py:103-112 runs two extra linears and an add, and for the attention output
+    projection all-gathers the whole [b, s, h] activation first, attention.py:690-701).
+
+    ``kind == "column"`` (q / k / v): W [N/tp, K], A [r/tp, K] (rank dimension TP-split, as in the checkpoint), B [N/tp, r].
+    Only the tiny [M, r] rank activations cross the TP group.  ``kind == "row"`` (attention output): W [N, K/tp],
+    A [r/tp, K_full], B [N, r/tp]; each rank multiplies ITS input columns with the matching columns of the gathered A, so
+    the low-rank term is a per-rank partial sum exactly like the base product and rides the same (fused) all-reduce —
+    the activation is never gathered.  dX = dY·W + dT·A is again one launch with [dY | dT] x [W ; A].
+    """
+
+    @staticmethod
+    def forward(ctx, x, W, A, B, scale, kind, tp, comm):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        size, rank, group = tp
+        if kind == "column":
+            t = _gather_dim(K.gemm(x2, A), 1, tp)  # [M, r]
+            ts = t * scale
+            y = K.gemm_lowrank(x2, W, ts, B)
+            ctx.save_for_backward(x2, W, A, B, ts)
+        else:
+            kl = x2.shape[1]
+            a_cols = _gather_dim(A, 0, tp)[:, rank * kl:(rank + 1) * kl].contiguous()  # [r, K/tp]
+            b_full = _gather_dim(B, 1, tp)  # [N, r]
+            ts = K.gemm(x2, a_cols) * scale  # this rank's partial of the rank activations
+            if size > 1 and comm is not None:
+                y = K.gemm_lowrank(x2, W, ts, b_full, comm=comm)
+            else:
+                y = K.gemm_lowrank(x2, W, ts, b_full)
+                if size > 1:
+                    torch.distributed.all_reduce(y, group=group)
+            ctx.save_for_backward(x2, W, a_cols, b_full, ts)
+        ctx.meta = (scale, kind, tp, comm, shape)
+        return y.view(*shape[:-1], W.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, W, A_, B_, ts = ctx.saved_tensors
+        scale, kind, tp, comm, shape = ctx.meta
+        size, rank, group = tp
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dts = K.gemm(dy2, B_, b_mn=True)  # [M, r]: dY·B
+        if kind == "column":
+            if size > 1:  # every rank's output used the full rank activations: sum, keep the own rank slice
+                torch.distributed.all_reduce(dts, group=group)
+                rl = dts.shape[1] // size
+                dts = dts[:, rank * rl:(rank + 1) * rl].contiguous()
+            dtl = dts * scale
+            dx = K.gemm_lowrank(dy2, W, dtl, A_, b_mn=True, comm=comm if size > 1 else None)
+            if size > 1 and comm is None:
+                torch.distributed.all_reduce(dx, group=group)
+            dB = K.gemm(dy2, ts, a_mn=True, b_mn=True)  # [N/tp, r]
+            dA = K.gemm(dtl, x2, a_mn=True, b_mn=True)  # [r/tp, K]
+        else:
+            dtl = dts * scale
+            dx = K.gemm_lowrank(dy2, W, dtl, A_, b_mn=True)  # [M, K/tp], no reduction: columns are rank-local
+            t_full = ts.clone()
+            if size > 1:
+                torch.distributed.all_reduce(t_full, group=group)
+            dB_full = K.gemm(dy2, t_full, a_mn=True, b_mn=True)  # [N, r]
+            rl = dB_full.shape[1] // size
+            dB = dB_full[:, rank * rl:(rank + 1) * rl].contiguous()
+            dA_cols = K.gemm(dtl, x2, a_mn=True, b_mn=True)  # [r, K/tp]
+            dA = _gather_dim(dA_cols, 1, tp)[rank * rl:(rank + 1) * rl].contiguous()  # own rank rows, all columns
+        dW = _accumulate_wgrad(dy2, x2, W) if ctx.needs_input_grad[1] else None
+        return dx.view(shape), dW, dA, dB, None, None, None, None
+
+
+_LORA_FUSED = os.environ.get("SCALING_B200_LORA_FUSED", "1") == "1"
+
+
+def lora_fusion_enabled() -> bool:
+    return _LORA_FUSED
+
+
+def set_lora_fusion(enabled: bool) -> None:
+    """A/B switch for tests and benchmarks: off = base GEMM plus separate LoRA linears (the reference's structure)."""
+    global _LORA_FUSED
+    _LORA_FUSED = bool(enabled)
+
+
+def lora_linear(x: torch.Tensor, W: torch.Tensor, A: torch.Tensor, B: torch.Tensor, scale: float, kind: str,
+                tp=(1, 0, None), comm=None) -> Optional[torch.Tensor]:
+    """LoRA-fused projection (see :class:`_LoraLinearFn`), or None when the shapes do not fit the 2-CTA kernel's
+    low-rank slab (the caller then adds the separate LoRA linears)."""
+    m = x.numel() // x.shape[-1] if x.numel() else 0
+    size = tp[0]
+    r_full = A.shape[0] * size
+    if not (native_enabled(x) and x.dtype == W.dtype == A.dtype == B.dtype == torch.bfloat16 and m >= 256
+            and W.shape[0] >= 128 and W.shape[1] >= 128 and _aligned(*W.shape) and A.shape[0] % 8 == 0
+            and r_full % 8 == 0 and _PLAIN_GEMM == "native"):
+        return None
+    return _LoraLinearFn.apply(x, W, A, B, float(scale), kind, tp, comm)
+
+
 # ------------------------------------------------------------------------------------------------ fused q|k|v etc.
 class _MultiLinearFn(torch.autograd.Function):
     """Several column-parallel projections of the same input as ONE GEMM each way.

@@ -119,6 +119,36 @@ def gemm(
     return out
 
 
+def gemm_lowrank(a: torch.Tensor, b: torch.Tensor, a2: torch.Tensor, b2: torch.Tensor, *, b_mn: bool = False,
+                 comm=None, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """D[M,N] = A·Bᵀ + A2·B2ᵀ in one launch: the low-rank pair (A2 [M,r]; B2 [N,r], or [r,N] when ``b_mn``) rides as
+    extra k-blocks behind the main K range of the 2-CTA tcgen05 GEMM.  With ``comm`` the result is additionally summed
+    over the tensor-parallel group inside the same launch (fused all-reduce)."""
+    assert all(t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1 for t in (a, b, a2, b2))
+    M, K = a.shape
+    N = b.shape[1] if b_mn else b.shape[0]
+    assert (b.shape[0] if b_mn else b.shape[1]) == K
+    r = a2.shape[1]
+    assert a2.shape[0] == M and (b2.shape == (r, N) if b_mn else b2.shape == (N, r)), (a2.shape, b2.shape, N, r)
+    assert M >= 256 and N >= 128 and r % 8 == 0, "the low-rank slab exists on the 2-CTA kernel only"
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    lds = (a.stride(0), b.stride(0), a2.stride(0), b2.stride(0), out.stride(0))
+    assert all(x % 8 == 0 for x in lds) and all(t.data_ptr() % 16 == 0 for t in (a, b, a2, b2, out))
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    _ensure_split_workspace(a.device)
+    if comm is None:
+        call("sb_gemm2_lowrank_bf16", ptr(a), ptr(b), ptr(a2), ptr(b2), ptr(out), ptr(bias), M, N, K, r, lds[0], lds[1],
+             lds[2], lds[3], lds[4], int(b_mn), 0, 0, 0)
+    else:
+        comm.reserve(M, N)
+        epoch, data_ptrs, flag_ptrs = comm.next_call()
+        call("sb_gemm2_allreduce_lowrank_bf16", ptr(a), ptr(b), ptr(a2), ptr(b2), ptr(out), ptr(bias), M, N, K, r, lds[0],
+             lds[1], lds[2], lds[3], lds[4], int(b_mn), data_ptrs, flag_ptrs, comm.rank, comm.size, epoch, comm.slot_bytes,
+             comm.flag_slot, 0)
+    return out
+
+
 def gemm_allreduce(a: torch.Tensor, b: torch.Tensor, comm, *, b_mn: bool = False, bias: Optional[torch.Tensor] = None,
                    out: Optional[torch.Tensor] = None, max_ctas: int = 0) -> torch.Tensor:
     """D[M,N] = Σ_ranks A_r · B_rᵀ (+ bias) in ONE launch: the tcgen05 GEMM pushes its partial tiles over NVLink into

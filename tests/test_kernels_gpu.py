@@ -361,3 +361,68 @@ def test_attention_sm100(causal, T, cu, heads, kv_heads):
     assert _rel_err(q.grad, qf.grad) < 3e-2, _rel_err(q.grad, qf.grad)
     assert _rel_err(k.grad, kf.grad) < 3e-2, _rel_err(k.grad, kf.grad)
     assert _rel_err(v.grad, vf.grad) < 3e-2, _rel_err(v.grad, vf.grad)
+
+
+def _max_rel_per_row(out: torch.Tensor, ref: torch.Tensor) -> float:
+    """Worst row: max-abs error of a row over that row's max-abs reference.  A few wrong rows in a tail tile barely
+    move a Frobenius ratio over a 4096^2 output; they do move this."""
+    out, ref = out.float(), ref.float()
+    err = (out - ref).abs().amax(dim=-1)
+    scale = ref.abs().amax(dim=-1).clamp_min(1e-6)
+    return float((err / scale).max())
+
+
+@pytest.mark.parametrize("M,N,K_", [(4096, 4096, 4096), (1000, 776, 520), (4096, 2048, 4096), (4096, 4096, 2048), (513, 257 * 8, 7168)])
+def test_gemm_per_row_error(M, N, K_):
+    from scaling_b200.ops import kernels as K
+
+    torch.manual_seed(11)
+    a = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(N, K_, device="cuda", dtype=torch.bfloat16) / math.sqrt(K_)
+    ref = a.float() @ b.float().t()
+    assert _max_rel_per_row(K.gemm(a, b, out_dtype=torch.float32), ref) < 2e-4
+    assert _max_rel_per_row(K.gemm(a, b), ref) < 2e-2
+    assert _max_rel_per_row(K.gemm(a, b.t().contiguous(), b_mn=True), ref) < 2e-2
+
+
+@pytest.mark.parametrize("M,N,K_,r", [(4096, 4096, 4096, 64), (1000, 776, 520, 16), (512, 1024, 4096, 192), (4096, 512, 2048, 8)])
+@pytest.mark.parametrize("b_mn", [False, True])
+def test_gemm_lowrank_slab(M, N, K_, r, b_mn):
+    """D = A·Bᵀ + A2·B2ᵀ in one launch (LoRA as extra k-blocks) against the fp32 expression."""
+    from scaling_b200.ops import kernels as K
+
+    torch.manual_seed(3)
+    a = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn((K_, N) if b_mn else (N, K_), device="cuda", dtype=torch.bfloat16) / math.sqrt(K_)
+    a2 = torch.randn(M, r, device="cuda", dtype=torch.bfloat16)
+    b2 = torch.randn((r, N) if b_mn else (N, r), device="cuda", dtype=torch.bfloat16) / math.sqrt(r)
+    B = b.float() if b_mn else b.float().t()
+    B2 = b2.float() if b_mn else b2.float().t()
+    ref = a.float() @ B + a2.float() @ B2
+    out = K.gemm_lowrank(a, b, a2, b2, b_mn=b_mn)
+    assert _rel_err(out, ref) < 1e-2 and _max_rel_per_row(out, ref) < 3e-2, (_rel_err(out, ref), _max_rel_per_row(out, ref))
+    # the slab really contributes: without it the result is far off
+    assert _rel_err(K.gemm(a, b, b_mn=b_mn), ref) > 0.3
+
+
+@pytest.mark.parametrize("kind", ["column", "row"])
+def test_lora_linear_matches_autograd_of_the_plain_expression(kind):
+    """Fused LoRA projection (forward and all four gradients) against torch autograd of y = x Wᵀ + s (x Aᵀ) Bᵀ."""
+    from scaling_b200.ops import functional as OF
+
+    torch.manual_seed(0)
+    M, Kd, N, r, s = 1024, 1024, 768, 32, 0.5
+    x = torch.randn(2, M // 2, Kd, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    W = (torch.randn(N, Kd, device="cuda") / math.sqrt(Kd)).bfloat16().requires_grad_(True)
+    A = (torch.randn(r, Kd, device="cuda") / math.sqrt(Kd)).bfloat16().requires_grad_(True)
+    B = (torch.randn(N, r, device="cuda") / math.sqrt(r)).bfloat16().requires_grad_(True)
+    y = OF.lora_linear(x, W, A, B, s, kind)
+    assert y is not None
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    got = [y.detach(), x.grad, W.grad, A.grad, B.grad]
+    xf, Wf, Af, Bf = (t.detach().float().requires_grad_(True) for t in (x, W, A, B))
+    yr = xf @ Wf.t() + s * (xf @ Af.t()) @ Bf.t()
+    yr.backward(dy.float())
+    for name, g, ref in zip(["y", "dx", "dW", "dA", "dB"], got, [yr.detach(), xf.grad, Wf.grad, Af.grad, Bf.grad]):
+        assert g is not None and _rel_err(g, ref) < 2e-2, (name, _rel_err(g, ref))
