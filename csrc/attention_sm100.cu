@@ -389,16 +389,30 @@ int make_map(CUtensorMap* m, const void* ptr, uint64_t width, uint64_t rows, uin
 // q: [T, heads, 128] with token pitch q_pitch (elements); k, v: [T, kv_heads, 128] with pitches k_pitch / v_pitch.
 // seg_start / seg_end: int32 [T] sequence bounds of every token (packed batches).  out: [T, heads, 128] contiguous,
 // lse: fp32 [heads, T].  scale: softmax scale (e.g. 1/sqrt(128)).
+//
+// sb_attention_fwd_ex generalises the key side: k, v hold Tk rows (Tk != T for KV-cache decoding, where the new queries
+// attend to cached keys), and with causal == 0 the two arrays are simply "row t attends to keys [seg_start[t],
+// seg_end[t])" in KEY index space — any mask whose bounds are non-decreasing along t: causal (seg_end[t] = t + 1),
+// right-aligned causal for decoding, sliding windows (seg_start[t] = max(sequence start, t - window)), documents.
+extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                                   const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
+                                   long long k_pitch, long long v_pitch, float scale, int causal, cudaStream_t stream);
 extern "C" int sb_attention_fwd(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                                 const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                                 long long v_pitch, float scale, int causal, cudaStream_t stream) {
+  return sb_attention_fwd_ex(q, k, v, out, lse, seg_start, seg_end, T, T, heads, kv_heads, q_pitch, k_pitch, v_pitch, scale,
+                             causal, stream);
+}
+extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                                   const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
+                                   long long k_pitch, long long v_pitch, float scale, int causal, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
-  if (heads % kv_heads) return -1;
+  if (heads % kv_heads || Tk <= 0 || (causal && Tk != T)) return -1;
   CUtensorMap mq, mk, mv;
   if (make_map(&mq, q, (uint64_t)heads * D, T, q_pitch)) return -2;
-  if (make_map(&mk, k, (uint64_t)kv_heads * D, T, k_pitch)) return -2;
-  if (make_map(&mv, v, (uint64_t)kv_heads * D, T, v_pitch)) return -2;
+  if (make_map(&mk, k, (uint64_t)kv_heads * D, Tk, k_pitch)) return -2;
+  if (make_map(&mv, v, (uint64_t)kv_heads * D, Tk, v_pitch)) return -2;
   Params p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale_log2 = scale * 1.4426950408889634f, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.out = (__nv_bfloat16*)out, p.lse = lse;
@@ -439,6 +453,7 @@ struct BwdParams {
   int causal;
   const int* seg_start;
   const int* seg_end;
+  const int* key_qend;  // optional [T]: one past the last query that sees key t (tighter than seg_end under a window)
   const float* lse2;    // [heads, Tp] lse · log2(e)   (Tp = padded pitch, multiple of 64 and > T)
   const float* delta;   // [heads, Tp] Σ_d dO·O
   int Tp;
@@ -562,7 +577,7 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
   const int kv_last = min(kv0 + 128, p.T) - 1;
   // queries that can see a key of this tile: same sequence(s), and not before the key when causal
   const int q_begin = ((p.causal ? kv0 : p.seg_start[kv0]) / BS) * BS;
-  const int q_end = p.seg_end[kv_last];
+  const int q_end = (p.key_qend ? p.key_qend : p.seg_end)[kv_last];
   const int n_sub = (q_end - q_begin + BS - 1) / BS;
   const int n_it = n_sub * group;
   // which query sub-tiles need element-wise masking against this key tile (diagonal, document edges, tails)
@@ -925,10 +940,27 @@ extern "C" long long sb_attention_bwd_scratch_floats(int T, int heads) {
 // dout, out: [T, heads, 128] contiguous; q/k/v as in sb_attention_fwd; lse: [heads, T] from the forward pass;
 // scratch: fp32 buffer of sb_attention_bwd_scratch_floats(T, heads) owned by the caller (must start zero-filled or at
 // least finite: the padding is read but masked); dq: [T, heads, 128], dk/dv: [T, kv_heads, 128] contiguous.
+//
+// sb_attention_bwd_ex: as sb_attention_bwd, plus key_qend (int32 [T], may be NULL): one past the last query row that can
+// see key t, non-decreasing — lets the dK/dV blocks stop early under a sliding window (the masks themselves come from
+// seg_start / seg_end, which the caller narrows per row).
+extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
+                                   const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
+                                   long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
+                                   cudaStream_t stream);
 extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
                                 const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
                                 const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                                 long long v_pitch, float scale, int causal, cudaStream_t stream) {
+  return sb_attention_bwd_ex(dout, q, k, v, out, lse, scratch, dq, dk, dv, seg_start, seg_end, nullptr, T, heads, kv_heads,
+                             q_pitch, k_pitch, v_pitch, scale, causal, stream);
+}
+extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
+                                   const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
+                                   long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
+                                   cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
   if (heads % kv_heads) return -1;
@@ -940,7 +972,7 @@ extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, 
                                                                       lse, lse2, delta, T, heads, Tp);
   BwdParams p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale = scale, p.scale_log2 = scale * kLog2e, p.causal = causal;
-  p.seg_start = seg_start, p.seg_end = seg_end, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
+  p.seg_start = seg_start, p.seg_end = seg_end, p.key_qend = key_qend, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
   p.dq = (__nv_bfloat16*)dq, p.dk = (__nv_bfloat16*)dk, p.dv = (__nv_bfloat16*)dv;
   static sb::PerDeviceOnce once;
   static bool separate = false;  // SCALING_B200_ATTN_BWD_SEPARATE=1: two launches (dK/dV, then dQ), for A/B timing

@@ -428,6 +428,83 @@ extern "C" int sb_embedding_fwd_peers(const long long* ids, const void* W, const
       ids, (const __nv_bfloat16*)W, o, tokens, hidden, vocab_start, vocab_end, seq, seq > 0 ? seq / tp : 0);
   return (int)cudaGetLastError();
 }
+// ---------------------------------------------------------------- sequence-parallel gather / reduce-scatter by peer stores
+// Megatron sequence parallelism moves [b, s/tp, h] <-> [b, s, h] around every column-/row-parallel block.  These kernels
+// do it with NVLink peer stores into symmetric exchange buffers instead of NCCL (reference
+// core/nn/linear/utils.py:279-305): the caller follows each launch with one device barrier.
+//   gather_push : every rank stores its [b, s_local, h] shard at sequence offset rank * s_local of EVERY rank's
+//                 [b, s, h] buffer;
+//   scatter_push: every rank stores slice j of its [b, s, h] partial sums into slot `rank` of rank j's
+//                 [tp, b, s_local, h] buffer; sum_slots then adds the tp slots in rank order (fp32 accumulate).
+__global__ void seq_gather_push_kernel(const uint4* __restrict__ src, EmbPeers outs, int rank, int s_local, int vec_per_row,
+                                       size_t total_vec) {
+  const int tp = outs.n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total_vec; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = i / vec_per_row, c = i % vec_per_row;
+    const size_t b = row / s_local, sl = row % s_local;
+    const size_t drow = b * ((size_t)s_local * tp) + (size_t)rank * s_local + sl;
+    const uint4 v = src[i];
+    for (int r = 0; r < tp; ++r) reinterpret_cast<uint4*>(outs.p[r])[drow * vec_per_row + c] = v;
+  }
+}
+__global__ void seq_scatter_push_kernel(const uint4* __restrict__ src, EmbPeers outs, int rank, int s_local, int vec_per_row,
+                                        size_t total_vec, size_t slot_vec) {
+  const int tp = outs.n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total_vec; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = i / vec_per_row, c = i % vec_per_row;
+    const size_t s = (size_t)s_local * tp;
+    const size_t b = row / s, pos = row % s;
+    const int owner = (int)(pos / s_local);
+    const size_t drow = b * s_local + pos % s_local;
+    reinterpret_cast<uint4*>(outs.p[owner])[(size_t)rank * slot_vec + drow * vec_per_row + c] = src[i];
+  }
+}
+__global__ void sum_slots_kernel(const uint4* __restrict__ slots, uint4* __restrict__ out, int tp, size_t slot_vec) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < slot_vec; i += (size_t)gridDim.x * blockDim.x) {
+    float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < tp; ++r) {
+      const uint4 x = slots[(size_t)r * slot_vec + i];
+      float2 a = sb::unpack_bf16(x.x), b = sb::unpack_bf16(x.y), c = sb::unpack_bf16(x.z), d = sb::unpack_bf16(x.w);
+      f[0] += a.x, f[1] += a.y, f[2] += b.x, f[3] += b.y, f[4] += c.x, f[5] += c.y, f[6] += d.x, f[7] += d.y;
+    }
+    out[i] = make_uint4(sb::pack_bf16(f[0], f[1]), sb::pack_bf16(f[2], f[3]), sb::pack_bf16(f[4], f[5]), sb::pack_bf16(f[6], f[7]));
+  }
+}
+static int fill_peers(EmbPeers& o, const unsigned long long* ptrs, int tp) {
+  if (tp < 1 || tp > 8) return -1;
+  o.n = tp;
+  for (int r = 0; r < tp; ++r) o.p[r] = reinterpret_cast<__nv_bfloat16*>(ptrs[r]);
+  return 0;
+}
+// src: [batch, s_local, hidden] bf16 contiguous; out_ptrs: tp peer-mapped [batch, s_local * tp, hidden] buffers
+extern "C" int sb_seq_gather_push(const void* src, const unsigned long long* out_ptrs, int tp, int rank, int batch,
+                                  int s_local, int hidden, cudaStream_t st) {
+  if (batch <= 0 || s_local <= 0) return 0;
+  if (hidden % 8) return -1;
+  EmbPeers o{};
+  if (fill_peers(o, out_ptrs, tp)) return -5;
+  const size_t total = (size_t)batch * s_local * (hidden / 8);
+  seq_gather_push_kernel<<<blocks_for(total), 256, 0, st>>>((const uint4*)src, o, rank, s_local, hidden / 8, total);
+  return (int)cudaGetLastError();
+}
+// src: [batch, s_local * tp, hidden] bf16 partial sums; out_ptrs: tp peer-mapped [tp, batch, s_local, hidden] slot buffers
+extern "C" int sb_seq_scatter_push(const void* src, const unsigned long long* out_ptrs, int tp, int rank, int batch,
+                                   int s_local, int hidden, cudaStream_t st) {
+  if (batch <= 0 || s_local <= 0) return 0;
+  if (hidden % 8) return -1;
+  EmbPeers o{};
+  if (fill_peers(o, out_ptrs, tp)) return -5;
+  const size_t slot = (size_t)batch * s_local * (hidden / 8);
+  seq_scatter_push_kernel<<<blocks_for(slot * tp), 256, 0, st>>>((const uint4*)src, o, rank, s_local, hidden / 8, slot * tp, slot);
+  return (int)cudaGetLastError();
+}
+// out[n] = Σ_r slots[r][n] (bf16, fp32 accumulate, rank order); n % 8 == 0
+extern "C" int sb_sum_slots(const void* slots, void* out, int tp, long long n, cudaStream_t st) {
+  if (n <= 0) return 0;
+  if (n % 8) return -1;
+  sum_slots_kernel<<<blocks_for((size_t)n / 8), 256, 0, st>>>((const uint4*)slots, (uint4*)out, tp, (size_t)n / 8);
+  return (int)cudaGetLastError();
+}
 extern "C" int sb_embedding_bwd(const long long* ids, const void* dout, void* dW, int grad_fp32, int tokens, int hidden,
                                 long long vocab_start, long long vocab_end, cudaStream_t st) {
   if (tokens <= 0) return 0;

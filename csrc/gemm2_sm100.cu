@@ -29,7 +29,7 @@ constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
 constexpr uint32_t kPeerMask = 0xFEFFFFFF;  // clears the CTA-rank bit of a shared::cluster address -> leader's copy
 
-enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3 };
+enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, kXentStats = 4 };
 
 // ---- fused all-reduce (kAllReduce) ----------------------------------------------------------------------------
 // One launch computes this rank's partial product AND the tensor-parallel sum of it.  Every rank owns a symmetric
@@ -615,7 +615,53 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         __threadfence();
       }
 
-      if (kEpi == kSwiGLU) {
+      if (kEpi == kXentStats) {
+        // LM head: store the bf16 logits AND the cross-entropy statistics of this row over the tile's 256 columns
+        // (max, Σexp(x - max), arg-max) while the accumulator is in registers — the forward never re-reads the logits
+        // (SURVEY §8 G8).  Statistics are taken from the bf16-rounded values, i.e. from exactly what is stored.
+        const int n0 = tn * BN;
+        __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd;
+        float m_run = -INFINITY, s_run = 0.f, best = -INFINITY;
+        int best_i = 0;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c, v);
+          tmem_ld_wait();
+          const int col = n0 + c;
+          if (!row_ok || col >= p.N) continue;
+          const int nv = min(32, p.N - col);
+          uint32_t packed[16];
+          float cm = -INFINITY;
+          int ci = 0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            packed[i] = pack_bf16(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+            const float2 f2 = unpack_bf16(packed[i]);
+            const float f0 = (2 * i < nv) ? f2.x : -INFINITY, f1 = (2 * i + 1 < nv) ? f2.y : -INFINITY;
+            v[2 * i] = __float_as_uint(f0), v[2 * i + 1] = __float_as_uint(f1);
+            if (f0 > cm) cm = f0, ci = 2 * i;
+            if (f1 > cm) cm = f1, ci = 2 * i + 1;
+          }
+          if (cm > best) best = cm, best_i = col + ci;
+          const float m_new = fmaxf(m_run, cm);
+          float sum = 0.f;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sum += __expf(__uint_as_float(v[i]) - m_new);
+          s_run = s_run * __expf(m_run - m_new) + sum;
+          m_run = m_new;
+          if (nv == 32) {
+            uint4* dst = reinterpret_cast<uint4*>(drow + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+          } else {
+            for (int i = 0; i < nv; ++i) drow[col + i] = __float2bfloat16(__uint_as_float(v[i]));
+          }
+        }
+        if (row_ok && n0 < p.N)
+          reinterpret_cast<float4*>(p.aux)[(size_t)row * p.tiles_n + tn] =
+              make_float4(m_run, s_run, 0.f, __int_as_float(best_i));
+      } else if (kEpi == kSwiGLU) {
         const int n0 = tn * (BN / 2);
         __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd;
         __nv_bfloat16* arow = p.aux ? reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux : nullptr;
@@ -853,7 +899,7 @@ static int launch(const Maps& m, Params& p, cudaStream_t stream, int max_ctas) {
   // Wave quantisation: 256 tiles on 74 clusters are 3.46 waves, i.e. the machine idles 13 % of the kernel.  Cut the
   // tiles of the last, partial wave along K so that they occupy (almost) every cluster; the parts meet in an fp32
   // workspace and the last one to arrive runs the epilogue on the sum.
-  if (EPI != kAllReduce && split_enabled()) {
+  if (EPI != kAllReduce && EPI != kXentStats && split_enabled()) {
     const int rem = tiles % width;
     const int k_blocks = (p.K + BK - 1) / BK + p.kb_extra;
     int parts = rem > 0 ? width / rem : 1;
@@ -944,6 +990,24 @@ extern "C" int sb_gemm2_lowrank_bf16(const void* A, const void* B, const void* A
                                      cudaStream_t stream) {
   LowRank lr{A2, B2, K2, lda2, ldb2};
   return gemm2_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, 0, b_layout, out_dtype, epilogue, &lr, max_ctas, stream);
+}
+
+// LM-head GEMM with the cross-entropy statistics in its epilogue: logits[M,N] = X·Wᵀ (bf16) and
+// stats[M, ceil(N/256)] float4 = per row and 256-column tile (max, Σexp(x - max), unused, local arg-max column as int
+// bits), taken from the stored bf16 values.  sb_xent_combine (xent.cu) merges the tiles, picks the target logit and
+// exchanges the per-token result across the tensor-parallel group.  Replaces F.linear + all-gather + fp32 copy +
+// cross_entropy (transformer/model/layers/lm_head_tied.py:41-43, transformer/model/model.py:56-76).
+extern "C" long long sb_gemm2_xent_tiles(int N) { return (N + BN - 1) / BN; }
+extern "C" int sb_gemm2_xent_stats_bf16(const void* X, const void* W, void* logits, float* stats, int M, int N, int K,
+                                        int ldx, int ldw, int ldl, int max_ctas, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  Params p{};
+  Maps m;
+  if (int rc = make_maps(m, X, W, M, N, K, ldx, ldw, 0, 0, nullptr, p)) return rc;
+  p.M = M, p.N = N, p.K = K, p.D = logits, p.ldd = ldl, p.aux = stats;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + BN - 1) / BN;
+  return launch<0, 0, kXentStats, __nv_bfloat16>(m, p, stream, max_ctas);
 }
 
 // Same contract as sb_gemm_swiglu_bf16: CTA 0 of the pair stages the gate rows, CTA 1 the up rows of the tile.

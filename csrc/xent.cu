@@ -123,8 +123,77 @@ __global__ void __launch_bounds__(kThreads) grad_kernel(T* __restrict__ logits, 
   }
 }
 
+// ---- statistics produced by the LM-head GEMM epilogue (gemm2_sm100.cu, kXentStats) -------------------------------
+// combine: one thread per token merges the per-tile partials of its row, picks the target logit out of the stored
+// logits and writes {max, Σexp, target logit, arg-max id} to slot `rank` of EVERY tensor-parallel rank's exchange
+// buffer (NVLink peer stores; own buffer when tp == 1).  finalize (after a group barrier): merges the tp slots into
+// the per-token loss, log-sum-exp and arg-max.
+struct StatPeers {
+  float4* p[8];
+  int n;
+};
+__global__ void combine_tiles_kernel(const float4* __restrict__ partial, int tiles, const __nv_bfloat16* __restrict__ logits,
+                                     long long ld, const long long* __restrict__ targets, int tokens, int vocab_local,
+                                     long long vocab_start, StatPeers outs, int rank) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tokens) return;
+  MS acc{-INFINITY, 0.f};
+  float best = -INFINITY;
+  int best_i = 0;
+  for (int j = 0; j < tiles; ++j) {
+    const float4 q = partial[(size_t)t * tiles + j];
+    acc = combine(acc, MS{q.x, q.y});
+    if (q.x > best) best = q.x, best_i = __float_as_int(q.w);  // a tile's max IS its arg-max value; ties keep the lower id
+  }
+  const long long tgt = targets[t] - vocab_start;
+  const float tl = (tgt >= 0 && tgt < vocab_local) ? __bfloat162float(logits[(size_t)t * ld + tgt]) : 0.f;
+  const float4 out = make_float4(acc.m, acc.s, tl, __int_as_float((int)(best_i + vocab_start)));
+  for (int r = 0; r < outs.n; ++r) outs.p[r][(size_t)rank * tokens + t] = out;
+}
+__global__ void finalize_kernel(const float4* __restrict__ all, int tp, int tokens, float* __restrict__ loss,
+                                float* __restrict__ lse, long long* __restrict__ argmax) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tokens) return;
+  MS acc{-INFINITY, 0.f};
+  float best = -INFINITY, tl = 0.f;
+  int best_i = 0;
+  for (int r = 0; r < tp; ++r) {
+    const float4 q = all[(size_t)r * tokens + t];
+    acc = combine(acc, MS{q.x, q.y});
+    tl += q.z;
+    if (q.x > best) best = q.x, best_i = __float_as_int(q.w);
+  }
+  const float l = acc.m + __logf(acc.s);
+  lse[t] = l;
+  loss[t] = l - tl;
+  argmax[t] = best_i;
+}
+
 }  // namespace xent
 }  // namespace sb
+
+// out_ptrs: tp peer-mapped addresses of a [tp, tokens] float4 exchange buffer (own included; for tp == 1 any local
+// buffer).  Follow with a group barrier and sb_xent_finalize on the local buffer.
+extern "C" int sb_xent_combine(const float* partial, int tiles, const void* logits, long long ld, const long long* targets,
+                               int tokens, int vocab_local, long long vocab_start, const unsigned long long* out_ptrs,
+                               int tp, int rank, cudaStream_t st) {
+  using namespace sb::xent;
+  if (tokens <= 0) return 0;
+  if (tp < 1 || tp > 8 || rank < 0 || rank >= tp) return -5;
+  StatPeers o{};
+  o.n = tp;
+  for (int r = 0; r < tp; ++r) o.p[r] = reinterpret_cast<float4*>(out_ptrs[r]);
+  combine_tiles_kernel<<<(tokens + 127) / 128, 128, 0, st>>>((const float4*)partial, tiles, (const __nv_bfloat16*)logits, ld,
+                                                            targets, tokens, vocab_local, vocab_start, o, rank);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_xent_finalize(const float* all, int tp, int tokens, float* loss, float* lse, long long* argmax,
+                                cudaStream_t st) {
+  using namespace sb::xent;
+  if (tokens <= 0) return 0;
+  finalize_kernel<<<(tokens + 127) / 128, 128, 0, st>>>((const float4*)all, tp, tokens, loss, lse, argmax);
+  return (int)cudaGetLastError();
+}
 
 // dtype: 0 bf16, 1 fp32.  ld = row pitch in elements (multiple of 8).
 extern "C" int sb_xent_stats(const void* logits, const long long* targets, float* stats, int tokens, int vocab_local,

@@ -64,9 +64,25 @@ def _shard_dim(x: torch.Tensor, dim: int, size: int, rank: int) -> torch.Tensor:
     return x.narrow(dim, rank * n, n).contiguous()
 
 
+def _peer_comm(x: torch.Tensor, group: Any):
+    """The TP group's peer-memory communicator when ``x`` can take the NVLink peer-store path (CUDA, bf16, [b, s, h])."""
+    if not x.is_cuda:
+        return None
+    from ...ops import kernels as K
+    from ...parallel.symm import comm_for_group
+
+    comm = comm_for_group(group)
+    return comm if K.seq_peer_ok(x, comm) else None
+
+
 def _reduce_scatter_seq(x: torch.Tensor, size: int, group: Any) -> torch.Tensor:
     """[b, s, h] -> [b, s/size, h], summed over the group. The sequence is dimension 1."""
     assert x.shape[1] % size == 0, "sequence length must be divisible by the tensor parallel size"
+    comm = _peer_comm(x, group)
+    if comm is not None:  # peer stores + device barrier + local sum (own kernels), no NCCL on the layer path
+        from ...ops import kernels as K
+
+        return K.seq_reduce_scatter(x, comm)
     # reduce_scatter_tensor splits dim 0 -> bring the sequence dim to the front
     xt = x.transpose(0, 1).contiguous()
     out = torch.empty((xt.shape[0] // size, *xt.shape[1:]), dtype=x.dtype, device=x.device)
@@ -75,6 +91,11 @@ def _reduce_scatter_seq(x: torch.Tensor, size: int, group: Any) -> torch.Tensor:
 
 
 def _all_gather_seq(x: torch.Tensor, size: int, group: Any) -> torch.Tensor:
+    comm = _peer_comm(x, group)
+    if comm is not None:
+        from ...ops import kernels as K
+
+        return K.seq_all_gather(x, comm)
     xt = x.transpose(0, 1).contiguous()
     out = torch.empty((xt.shape[0] * size, *xt.shape[1:]), dtype=x.dtype, device=x.device)
     dist.all_gather_into_tensor(out, xt, group=group)

@@ -47,9 +47,19 @@ _SIGS = {
     "sb_embedding_fwd": [P, P, P, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_fwd_peers": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_int, P],
+    "sb_seq_gather_push": [P, P, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_seq_scatter_push": [P, P, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_sum_slots": [P, P, c_int, c_longlong, P],
     "sb_xent_stats": [P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
+    "sb_gemm2_xent_stats_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_xent_combine": [P, c_int, P, c_longlong, P, c_int, c_int, c_longlong, P, c_int, c_int, P],
+    "sb_xent_finalize": [P, c_int, c_int, P, P, P, P],
     "sb_xent_grad": [P, P, P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_attention_fwd": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float, c_int, P],
+    "sb_attention_fwd_ex": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float,
+                            c_int, P],
+    "sb_attention_bwd_ex": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
+                            c_float, c_int, P],
     "sb_attention_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
                          c_float, c_int, P],
     "sb_grad_sumsq": [P, c_longlong, c_int, P, P, c_int, P, P],
@@ -69,6 +79,7 @@ _RET_LL = {
     "sb_gather_window_i32": [P, P, P, c_int, P, c_longlong],
     "sb_gemm2_allreduce_slot_bytes": [c_int, c_int],
     "sb_gemm2_split_workspace_bytes": [],
+    "sb_gemm2_xent_tiles": [c_int],
 }
 _RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int],
                      "sb_gemm2_set_split_workspace": [P, c_ulonglong], "sb_gemm2_set_profile_buffer": [P]}

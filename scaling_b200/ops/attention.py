@@ -4,10 +4,12 @@
 
 Paths, selected by device and shape (not a user-visible backend switch):
   * ``sm100``  — the hand-written sm_100a kernel (csrc/attention_sm100.cu: tcgen05 QKᵀ / PV with TMEM accumulators,
-                 online softmax in fp32, causal + varlen + GQA), used for bf16, head_dim 64/128 on a B200;
+                 online softmax in fp32; causal / bidirectional, packed sequences, GQA/MQA, sliding windows, KV-cache
+                 decoding), used for bf16 with head_dim <= 128 on a B200;
   * ``dense``  — plain PyTorch expression with an explicit mask: the oracle, the CPU path, and the only path that
                  supports attention-score manipulation (reference core/nn/attention/attention.py:96-201);
-  * ``flash``  — the flash-attn wheel, kept as the library baseline for A/B measurements (reference :204-259).
+  * ``flash``  — the flash-attn wheel, only when selected by name: the library baseline for A/B measurements
+                 (reference :204-259).  ``auto`` never picks it.
 """
 from __future__ import annotations
 
@@ -119,14 +121,15 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: t
         if fusable:
             from .attention_sm100 import sm100_attention_supported
 
+            # no library kernel behind "auto": what the sm_100a kernel does not cover (attention-probability dropout,
+            # fp16, head dims above 128, gradients through a KV cache) runs the plain PyTorch expression; the flash-attn
+            # wheel is only used when asked for by name (SCALING_B200_ATTENTION=flash, A/B measurements)
             if sm100_attention_supported(q, k, v, cu_seqlens_q, cu_k, causal, window, p):
                 impl = "sm100"
-            elif _flash():
-                impl = "flash"
     if impl == "sm100" and fusable:
         from .attention_sm100 import sm100_attention
 
-        return sm100_attention(q, k, v, cu_seqlens_q, max_seqlen_q, causal, scale)
+        return sm100_attention(q, k, v, cu_seqlens_q, max_seqlen_q, causal, scale, window=window, cu_seqlens_k=cu_k)
     if impl == "flash" and fusable and _flash():
         w = (-1, -1) if not window else (window, 0 if causal else window)
         return _flash()(q.contiguous(), k.contiguous(), v.contiguous(), cu_seqlens_q=cu_seqlens_q.to(torch.int32),

@@ -13,13 +13,24 @@ _BWD_IMPL = os.environ.get("SCALING_B200_ATTENTION_BWD", "auto")  # auto | sm100
 
 
 def sm100_attention_supported(q, k, v, cu_q, cu_k, causal, window, dropout_p) -> bool:
+    """bf16, head dim <= 128 (smaller heads are zero-padded to the kernel's 128), GQA/MQA, packed sequences, causal or
+    bidirectional, sliding windows; keys may differ from queries (KV-cache decoding) when no gradient is needed.
+    Attention-probability dropout is not implemented in the kernel."""
     lib = _lib.load() if torch.cuda.is_available() else None
-    if lib is None or not hasattr(lib, "sb_attention_fwd"):
+    if lib is None or not hasattr(lib, "sb_attention_fwd_ex"):
         return False
-    return (q.dtype == torch.bfloat16 and q.shape[-1] == 128 and not window and dropout_p == 0.0 and cu_q is cu_k
-            and q.shape[1] % k.shape[1] == 0 and q.stride(2) == 1 and q.stride(1) == 128 and k.stride(2) == 1
-            and k.stride(1) == 128 and v.stride(2) == 1 and v.stride(1) == 128 and q.stride(0) % 8 == 0
-            and k.stride(0) % 8 == 0 and v.stride(0) % 8 == 0)
+    d = q.shape[-1]
+    if not (q.dtype == torch.bfloat16 and d <= 128 and d % 8 == 0 and dropout_p == 0.0 and q.shape[1] % k.shape[1] == 0):
+        return False
+    if cu_q is not cu_k and (q.requires_grad or k.requires_grad or v.requires_grad) and torch.is_grad_enabled():
+        return False  # decoding against a cache is forward only
+    if cu_q is not cu_k and (cu_q.numel() != 2 or cu_k.numel() != 2):
+        return False  # one sequence (the reference's KV cache is batch size 1 as well)
+    return True
+
+
+def _strided_ok(t: torch.Tensor) -> bool:
+    return t.stride(2) == 1 and t.stride(1) == 128 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
 
 
 _bounds_cache: "OrderedDict[tuple, tuple]" = None  # type: ignore[assignment]
@@ -57,12 +68,24 @@ def segment_bounds(cu_seqlens: torch.Tensor, total: int) -> Tuple[torch.Tensor, 
     return start, end
 
 
+def window_bounds(cu_seqlens: torch.Tensor, total: int, causal: bool, window: int):
+    """Per-token key bounds under a sliding window of ``window`` tokens to the left (and, when not causal, to the right):
+    (lo, hi, key_qend) int32 [total].  Row t sees keys [lo[t], hi[t]) — the kernels take these in place of the sequence
+    bounds — and key t is seen by queries up to key_qend[t] (lets the dK/dV blocks stop early)."""
+    start, end = segment_bounds(cu_seqlens, total)
+    pos = torch.arange(total, device=start.device, dtype=torch.int32)
+    lo = torch.maximum(start, pos - window)
+    qend = torch.minimum(end, pos + window + 1)
+    hi = end if causal else qend
+    return lo.contiguous(), hi.contiguous(), qend.contiguous()
+
+
 def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float):
     T, heads, d = q.shape
     out = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     lse = torch.empty((heads, T), dtype=torch.float32, device=q.device)
-    call("sb_attention_fwd", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, heads, k.shape[1],
-         q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal))
+    call("sb_attention_fwd_ex", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, k.shape[0],
+         heads, k.shape[1], q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal))
     return out, lse
 
 
@@ -88,38 +111,43 @@ def has_native_bwd() -> bool:
     return lib is not None and hasattr(lib, "sb_attention_bwd")
 
 
-def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, scale: float):
+def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, scale: float, key_qend=None):
     T, heads, d = q.shape
     kvh = k.shape[1]
     dq = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     dk = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     dv = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     delta = _bwd_scratch(q.device, T, heads)
-    call("sb_attention_bwd", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
-         ptr(seg_start), ptr(seg_end), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
+    call("sb_attention_bwd_ex", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
+         ptr(seg_start), ptr(seg_end), ptr(key_qend), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
          launches=3)
     return dq, dk, dv
 
 
 class AttentionFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, cu_seqlens, max_seqlen, causal, scale):
-        seg_start, seg_end = segment_bounds(cu_seqlens, q.shape[0])
+    def forward(ctx, q, k, v, cu_seqlens, max_seqlen, causal, scale, window):
+        if window:
+            seg_start, seg_end, key_qend = window_bounds(cu_seqlens, q.shape[0], causal, int(window))
+        else:
+            seg_start, seg_end = segment_bounds(cu_seqlens, q.shape[0])
+            key_qend = None
         out, lse = attention_fwd(q, k, v, seg_start, seg_end, causal, scale)
         ctx.save_for_backward(q, k, v, out, lse, seg_start, seg_end, cu_seqlens)
-        ctx.args = (max_seqlen, causal, scale)
+        ctx.key_qend = key_qend
+        ctx.args = (max_seqlen, causal, scale, window)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse, seg_start, seg_end, cu = ctx.saved_tensors
-        max_seqlen, causal, scale = ctx.args
+        max_seqlen, causal, scale, window = ctx.args
         dout = dout.contiguous()
         impl = _BWD_IMPL
         if impl == "auto":
             impl = "sm100" if has_native_bwd() else "flash"
         if impl == "sm100":
-            dq, dk, dv = attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal, scale)
+            dq, dk, dv = attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal, scale, ctx.key_qend)
         else:
             # library backward on this kernel's forward results (same LSE convention: natural log, [heads, tokens])
             from flash_attn.flash_attn_interface import _flash_attn_varlen_backward
@@ -127,10 +155,32 @@ class AttentionFn(torch.autograd.Function):
             qc, kc, vc = q.contiguous(), k.contiguous(), v.contiguous()
             dq, dk, dv = torch.empty_like(qc), torch.empty_like(kc), torch.empty_like(vc)
             cu32 = cu.to(torch.int32)
+            w = (-1, -1) if not window else (int(window), 0 if causal else int(window))
             _flash_attn_varlen_backward(dout, qc, kc, vc, out, lse, dq, dk, dv, cu32, cu32, max_seqlen, max_seqlen, 0.0,
-                                        scale, causal, -1, -1, 0.0, None, False, None)
-        return dq, dk, dv, None, None, None, None
+                                        scale, causal, w[0], w[1], 0.0, None, False, None)
+        return dq, dk, dv, None, None, None, None, None
 
 
-def sm100_attention(q, k, v, cu_seqlens, max_seqlen, causal, scale):
-    return AttentionFn.apply(q, k, v, cu_seqlens, max_seqlen, causal, scale)
+def _decode_forward(q, k, v, causal, scale, window):
+    """Queries of ONE sequence against a longer key/value cache (right-aligned causal mask), forward only."""
+    tq, tk = q.shape[0], k.shape[0]
+    pos = torch.arange(tq, device=q.device, dtype=torch.int32) + (tk - tq)  # key index of each query token
+    hi = (pos + 1) if causal else torch.full_like(pos, tk)
+    lo = torch.clamp(pos - int(window), min=0) if window else torch.zeros_like(pos)
+    if window and not causal:
+        hi = torch.clamp(pos + int(window) + 1, max=tk)
+    out, _ = attention_fwd(q, k, v, lo.contiguous(), hi.contiguous(), False, scale)
+    return out
+
+
+def sm100_attention(q, k, v, cu_seqlens, max_seqlen, causal, scale, window=None, cu_seqlens_k=None):
+    d = q.shape[-1]
+    if d < 128:  # the kernel's tiles are 128 wide: zero columns change neither the scores nor the first d outputs
+        pad = (0, 128 - d)
+        q, k, v = (torch.nn.functional.pad(t, pad) for t in (q, k, v))
+    q, k, v = (t if _strided_ok(t) else t.contiguous() for t in (q, k, v))
+    if cu_seqlens_k is not None and cu_seqlens_k is not cu_seqlens:
+        out = _decode_forward(q, k, v, causal, scale, window)
+    else:
+        out = AttentionFn.apply(q, k, v, cu_seqlens, max_seqlen, causal, scale, window or None)
+    return out[..., :d] if d < 128 else out

@@ -701,10 +701,10 @@ class _EmbeddingPeersFn(torch.autograd.Function):
         w = ctx.weight_ref
         dout = dout.contiguous()
         if ctx.sp is not None:  # gradient of the scatter along the sequence: gather it back (dim 1)
+            from ..core.nn.tp_ops import _all_gather_seq
+
             size, group = ctx.sp
-            parts = torch.empty((size, *dout.shape), dtype=dout.dtype, device=dout.device)
-            torch.distributed.all_gather_into_tensor(parts, dout, group=group)
-            dout = torch.cat(list(parts.unbind(0)), dim=-2).contiguous()
+            dout = _all_gather_seq(dout, size, group)
         main = getattr(w, "main_grad", None)
         if main is not None:
             K.embedding_bwd(ids, dout, main, *ctx.range)
@@ -776,7 +776,75 @@ class _VocabParallelXentFn(torch.autograd.Function):
         return logits, None, None, None
 
 
-def vocab_parallel_cross_entropy(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int = 0, group=None):
+class _LinearXentStatsFn(torch.autograd.Function):
+    """LM-head projection whose GEMM epilogue also emits the cross-entropy statistics of every 256-column tile
+    (``sb_gemm2_xent_stats_bf16``): returns (logits, partial statistics).  Gradients as :class:`_LinearFn`."""
+
+    @staticmethod
+    def forward(ctx, x, weight, comm):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y, partial = K.gemm_xent_stats(x2, weight)
+        ctx.comm = comm
+        ctx.save_for_backward(x2, weight)
+        ctx.x_shape = shape
+        ctx.mark_non_differentiable(partial)
+        return y.view(*shape[:-1], weight.shape[0]), partial
+
+    @staticmethod
+    def backward(ctx, dy, _dpartial):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = (_gemm_nn_reduce(dy2, weight, ctx.comm) if ctx.comm is not None else _gemm_nn(dy2, weight)).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            dw = _accumulate_wgrad(dy2, x2, weight)
+        return dx, dw, None
+
+
+def linear_with_xent_stats(x: torch.Tensor, weight: torch.Tensor, comm=None):
+    """(logits, partial CE statistics) in one GEMM launch, or None when the epilogue kernel does not apply.  ``comm``:
+    sum dX over the TP group inside the dgrad GEMM, as in :func:`linear`."""
+    m = x.numel() // x.shape[-1] if x.numel() else 0
+    if not (native_enabled(x) and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and m >= 256
+            and weight.shape[0] >= 128 and _aligned(*weight.shape) and _PLAIN_GEMM == "native"):
+        return None
+    return _LinearXentStatsFn.apply(x, weight, comm)
+
+
+class _XentFromStatsFn(torch.autograd.Function):
+    """Cross-entropy on top of the LM-head epilogue statistics: forward never reads the logits again (only the one
+    target logit per token); backward overwrites them in place with (softmax − onehot)·dloss."""
+
+    @staticmethod
+    def forward(ctx, logits, partial, targets, vocab_start, comm):
+        targets = targets.contiguous()
+        loss, lse, argmax = K.xent_from_partials(partial, logits, targets, vocab_start, comm)
+        ctx.save_for_backward(logits, targets, lse)
+        ctx.vocab_start = vocab_start
+        ctx.mark_non_differentiable(argmax)
+        return loss, argmax
+
+    @staticmethod
+    def backward(ctx, dloss, _dargmax):
+        logits, targets, lse = ctx.saved_tensors
+        K.xent_grad_(logits, targets, lse, dloss.float().contiguous(), None, ctx.vocab_start)
+        return logits, None, None, None, None
+
+
+def vocab_parallel_cross_entropy(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int = 0, group=None,
+                                 partial: Optional[torch.Tensor] = None, comm=None):
+    if partial is not None and logits.dim() == 2 and logits.is_contiguous():
+        return _XentFromStatsFn.apply(logits, partial, targets, vocab_start, comm)
+    return _vocab_parallel_cross_entropy(logits, targets, vocab_start, group)
+
+
+def _vocab_parallel_cross_entropy(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int = 0, group=None):
     """logits: [tokens, V_local] (this rank's shard), targets: [tokens] global ids → (loss [tokens] fp32, argmax [tokens]).
     NOTE: the backward pass reuses the logits buffer for the gradient."""
     if native_enabled(logits) and logits.dtype in (torch.bfloat16, torch.float32) and logits.stride(-1) == 1 \

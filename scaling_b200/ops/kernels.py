@@ -377,7 +377,85 @@ def embedding_bwd(ids: torch.Tensor, dout: torch.Tensor, dweight: torch.Tensor, 
          dweight.shape[1], vocab_start, vocab_end)
 
 
+# ----------------------------------------------------------------------------------------------------------- sequence parallel
+def seq_peer_ok(x: torch.Tensor, comm) -> bool:
+    return (comm is not None and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 3 and x.shape[-1] % 8 == 0
+            and x.numel() > 0)
+
+
+def seq_all_gather(x: torch.Tensor, comm) -> torch.Tensor:
+    """[b, s/tp, h] -> [b, s, h]: every rank stores its shard into every rank's exchange buffer over NVLink
+    (``sb_seq_gather_push``), one device barrier, and the result is copied out of the (double-buffered) exchange buffer."""
+    b, sl, h = x.shape
+    x = x.contiguous()
+    buf, ptrs = comm.exchange_buffer("seq_gather", b * sl * comm.size * h * 2)
+    call("sb_seq_gather_push", ptr(x), ptrs, comm.size, comm.rank, b, sl, h)
+    comm.barrier()
+    return buf.view(torch.bfloat16).view(b, sl * comm.size, h).clone()
+
+
+def seq_reduce_scatter(x: torch.Tensor, comm) -> torch.Tensor:
+    """[b, s, h] partial sums -> [b, s/tp, h] summed over the group: slice j goes to rank j's slot buffer
+    (``sb_seq_scatter_push``), one device barrier, then the tp slots are added in rank order (``sb_sum_slots``)."""
+    b, s, h = x.shape
+    tp = comm.size
+    assert s % tp == 0
+    sl = s // tp
+    x = x.contiguous()
+    buf, ptrs = comm.exchange_buffer("seq_scatter", tp * b * sl * h * 2)
+    call("sb_seq_scatter_push", ptr(x), ptrs, tp, comm.rank, b, sl, h)
+    comm.barrier()
+    out = torch.empty((b, sl, h), dtype=torch.bfloat16, device=x.device)
+    call("sb_sum_slots", ptr(buf), ptr(out), tp, b * sl * h)
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------- cross-entropy
+def gemm_xent_stats(x: torch.Tensor, w: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """LM-head GEMM with the cross-entropy statistics in its epilogue: (logits [M, N] bf16, partial [M, ceil(N/256), 4]
+    fp32 = per 256-column tile (max, Σexp(x − max), unused, local arg-max column as int bits))."""
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 2 and w.dim() == 2
+    assert x.stride(1) == 1 and w.stride(1) == 1 and x.shape[1] == w.shape[1]
+    M, Kd = x.shape
+    N = w.shape[0]
+    assert M >= 256 and N >= 128 and gemm_supported(M, N, Kd, x.stride(0), w.stride(0), N)
+    lib = _lib.load(required=True)
+    logits = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    partial = torch.empty((M, int(lib.sb_gemm2_xent_tiles(N)), 4), dtype=torch.float32, device=x.device)
+    _ensure_split_workspace(x.device)
+    call("sb_gemm2_xent_stats_bf16", ptr(x), ptr(w), ptr(logits), ptr(partial), M, N, Kd, x.stride(0), w.stride(0), N, 0)
+    return logits, partial
+
+
+def xent_from_partials(partial: torch.Tensor, logits: torch.Tensor, targets: torch.Tensor, vocab_start: int,
+                       comm=None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """(loss, lse, argmax) per token from the epilogue statistics: tiles are merged and the target logit picked by one
+    small kernel that stores the per-token result into every TP rank's exchange buffer (16 bytes per token over
+    NVLink), a device barrier, and a finalize kernel — no NCCL, no torch glue."""
+    tokens, tiles, _ = partial.shape
+    tp = 1 if comm is None else comm.size
+    rank = 0 if comm is None else comm.rank
+    dev = partial.device
+    if comm is None:
+        import ctypes
+
+        allstats = torch.empty((1, tokens, 4), dtype=torch.float32, device=dev)
+        ptrs = (ctypes.c_ulonglong * 1)(allstats.data_ptr())
+    else:
+        buf, ptrs = comm.exchange_buffer("xent", tp * tokens * 16)
+        allstats = buf.view(torch.float32).view(tp, tokens, 4)
+    call("sb_xent_combine", ptr(partial), tiles, ptr(logits), logits.stride(0), ptr(targets), tokens, logits.shape[1],
+         vocab_start, ptrs, tp, rank)
+    if comm is not None:
+        comm.barrier()
+    loss = torch.empty(tokens, dtype=torch.float32, device=dev)
+    lse = torch.empty(tokens, dtype=torch.float32, device=dev)
+    argmax = torch.empty(tokens, dtype=torch.int64, device=dev)
+    call("sb_xent_finalize", ptr(allstats), tp, tokens, ptr(loss), ptr(lse), ptr(argmax))
+    return loss, lse, argmax
+
+
+
 def xent_stats(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int) -> torch.Tensor:
     """[tokens, 4] fp32: local max, local Σexp(x-max), target logit (0 if remote), local argmax (int bits)."""
     tokens, v = logits.shape

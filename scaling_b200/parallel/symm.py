@@ -227,6 +227,16 @@ class SymmetricArena:
         return arr(*[p + element_offset * self.itemsize for p in self.peer_ptrs])
 
 
+def comm_for_group(group: Any) -> Optional[TPComm]:
+    """The already-created communicator of a process group (None when the fused paths are off or not set up)."""
+    if not _ENABLED or group is None:
+        return None
+    for comm in _COMMS.values():
+        if comm.group is group:
+            return comm
+    return None
+
+
 def get_tp_comm(topology: Any, sequence_parallel: bool = False) -> Optional[TPComm]:
     """The fused-collective communicator of ``topology``'s TP group, or None when the fused path does not apply
     (single TP rank, CPU / gloo, disabled by SCALING_B200_FUSED_TP=0).  Plain tensor parallelism uses it for the fused

@@ -342,6 +342,28 @@ class TransformerLayer(TransformerLayerBaseIO):
             h = gather_from_sequence_parallel_region(h, self.topology)
         return adapter(h)
 
+    # The two halves of the block as separate calls (public in the reference, layer.py:189-239; its backward-compatibility
+    # test drives them one by one).  ``forward`` below is the fused form of ``mlp_block(attention_block(h))``.
+    def attention_block(self, hidden_state: torch.Tensor, cumulative_seq_lengths: Optional[torch.Tensor],
+                        position_ids: Optional[torch.Tensor], use_cache: bool = False, reset_cache: bool = False,
+                        cache_index: int = 0, attention_scores_manipulation: Optional[torch.Tensor] = None,
+                        attentions_score_manipulation_log_additive: Any = True) -> torch.Tensor:
+        a = self.self_attention(self.input_layernorm(hidden_state), cumulative_seq_lengths=cumulative_seq_lengths,
+                                position_ids=position_ids, use_cache=use_cache, reset_cache=reset_cache,
+                                cache_index=cache_index, attention_scores_manipulation=attention_scores_manipulation,
+                                attentions_score_manipulation_log_additive=attentions_score_manipulation_log_additive)
+        h = hidden_state + _dropout(a, self.p_attn, self.training, self.topology)
+        if hasattr(self, "attn_adapter_name"):
+            h = h + self._adapter(h, self.attn_adapter_name)
+        return h
+
+    def mlp_block(self, hidden_state: torch.Tensor) -> torch.Tensor:
+        m = self.mlp(self.post_attention_layernorm(hidden_state))
+        h = hidden_state + _dropout(m, self.p_mlp, self.training, self.topology)
+        if hasattr(self, "mlp_adapter_name"):
+            h = h + self._adapter(h, self.mlp_adapter_name)
+        return h
+
     def forward(self, x: TransformerLayerIO) -> TransformerLayerIO:
         s = x.inference_settings
         use_cache, reset_cache, cache_index, log_add = (False, False, 0, True) if s is None else \
@@ -410,6 +432,17 @@ class _LMHeadBase(TransformerLayerBaseIO):
         h = x.activations
         w = self._weight()
         comm = get_tp_comm(topo) if h.is_cuda else None
+        training = self.training and torch.is_grad_enabled()
+        fused = None
+        if training and (tp == 1 or comm is not None):
+            # CE statistics in the GEMM epilogue: the loss never re-reads the logits
+            fused = OF.linear_with_xent_stats(h, w, comm=comm)
+        if fused is not None:
+            logits, partial = fused
+            out = x.derive(logits)
+            start = 0 if topo is None else topo.model_parallel_rank * w.shape[0]
+            out.vocab_parallel_logits = (start, None if tp == 1 else topo.model_parallel_group, partial, comm)
+            return out
         if comm is not None:
             logits = OF.linear(h, w, None, comm=comm, reduce_input_grad=True)
         else:

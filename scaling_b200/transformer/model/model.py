@@ -56,7 +56,9 @@ def loss_function(output: TransformerLayerIO, batch: TextDatasetBatch) -> Tuple[
     logits = output.activations.reshape(-1, output.activations.shape[-1])
     shard = getattr(output, "vocab_parallel_logits", None)
     if shard is not None:
-        losses, argmax = OF.vocab_parallel_cross_entropy(logits, targets, vocab_start=shard[0], group=shard[1])
+        partial, comm = (shard[2], shard[3]) if len(shard) > 2 else (None, None)
+        losses, argmax = OF.vocab_parallel_cross_entropy(logits, targets, vocab_start=shard[0], group=shard[1],
+                                                         partial=partial, comm=comm)
     else:
         lf = logits.float()
         losses = torch.nn.functional.cross_entropy(lf, targets, reduction="none")

@@ -302,6 +302,35 @@ def test_dp_reduce_kernels_and_device_barrier_under_launch_skew():
     assert all(dist_launcher(_dp_kernel_stress_worker, world_size=2, timeout=300).values())
 
 
+def _lora_worker(rank: int, world_size: int, master_port: int, config_dict, fused: bool):
+    from scaling_b200.core import LaunchConfig
+    from scaling_b200.ops import functional as OF
+    from scaling_b200.transformer.train import main
+
+    OF.set_lora_fusion(fused)
+    launch = LaunchConfig(master_port=master_port, master_addr="127.0.0.1", world_size=world_size, global_rank=rank,
+                          local_slot=rank, payload=config_dict)
+    metrics = main(launch, return_metrics=True)
+    return [m["training/loss"] for m in (metrics or [])]
+
+
+@pytest.mark.parametrize("mp", [1, 2])
+def test_lora_fused_projections_match_separate_lora_linears(tmp_path, mp):
+    """LoRA on q/k/v/dense trained with the low-rank pair inside the projection GEMMs (extra K-slab, and for the output
+    projection inside the fused all-reduce, no activation gather) against base GEMM + separate LoRA linears."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=1024, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
+         "sequence_length": 256, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"},
+         "lora_config": {"name": "lo", "rank": 16, "alpha": 32}}
+    cfg = tiny_config(prefix, mp=mp, iters=6, gas=2, arch=a)
+    fused = dist_launcher(_lora_worker, world_size=mp, timeout=400, config_dict=cfg, fused=True)[0]
+    plain = dist_launcher(_lora_worker, world_size=mp, timeout=400, config_dict=cfg, fused=False)[0]
+    assert len(fused) == 6 and all(x == x for x in fused) and fused[-1] < fused[0]
+    for x, y in zip(fused, plain):
+        assert abs(x - y) / abs(y) < 2e-2, (fused, plain)
+
+
 def test_sequence_parallel_fused_reduce_scatter_matches_nccl(tmp_path):
     """Sequence-parallel TP=2 training with the row-parallel reduce-scatters inside the GEMM launch against the same
     run on NCCL reduce-scatters."""

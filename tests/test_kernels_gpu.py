@@ -351,7 +351,7 @@ def test_attention_sm100(causal, T, cu, heads, kv_heads):
     v = torch.randn(T, kv_heads, 128, device=dev, dtype=torch.bfloat16, requires_grad=True)
     cu_t = torch.tensor(cu, device=dev, dtype=torch.int32)
     scale = 1.0 / math.sqrt(128)
-    out = AttentionFn.apply(q, k, v, cu_t, max(b - a for a, b in zip(cu[:-1], cu[1:])), causal, scale)
+    out = AttentionFn.apply(q, k, v, cu_t, max(b - a for a, b in zip(cu[:-1], cu[1:])), causal, scale, None)
     qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
     ref = attention_dense(qf, kf, vf, cu_t, cu_t, causal, scale)
     assert _rel_err(out, ref) < 2e-2, _rel_err(out, ref)
@@ -426,3 +426,91 @@ def test_lora_linear_matches_autograd_of_the_plain_expression(kind):
     yr.backward(dy.float())
     for name, g, ref in zip(["y", "dx", "dW", "dA", "dB"], got, [yr.detach(), xf.grad, Wf.grad, Af.grad, Bf.grad]):
         assert g is not None and _rel_err(g, ref) < 2e-2, (name, _rel_err(g, ref))
+
+
+@pytest.mark.parametrize("M,N,K_", [(4096, 32000, 1024), (512, 1000, 256), (1000, 16000, 512), (256, 128, 64)])
+def test_lm_head_gemm_with_cross_entropy_statistics_in_the_epilogue(M, N, K_):
+    """Logits + per-tile CE statistics from ONE GEMM launch, merged by the combine / finalize kernels, against
+    F.cross_entropy on the fp32 copy of the same bf16 logits; gradient through the in-place (softmax - onehot) kernel."""
+    from scaling_b200.ops import functional as OF
+    from scaling_b200.ops import kernels as K
+
+    torch.manual_seed(1)
+    x = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    w = (torch.randn(N, K_, device="cuda") * (2.0 / math.sqrt(K_))).bfloat16().requires_grad_(True)
+    targets = torch.randint(0, N, (M,), device="cuda")
+    logits_ref = K.gemm(x.detach(), w.detach())
+    out = OF.linear_with_xent_stats(x, w)
+    assert out is not None
+    logits, partial = out
+    assert torch.equal(logits.detach(), logits_ref), "the statistics epilogue must store the same bf16 logits"
+    loss, argmax = OF.vocab_parallel_cross_entropy(logits, targets, partial=partial)
+    lf = logits_ref.float()
+    ref = torch.nn.functional.cross_entropy(lf, targets, reduction="none")
+    assert float((loss - ref).abs().max()) < 2e-3, float((loss - ref).abs().max())
+    # arg-max: equal, or a tie in value (bf16 logits tie often at large N)
+    am_ref = lf.argmax(-1)
+    bad = argmax != am_ref
+    assert bool((lf.gather(1, argmax[:, None]) == lf.gather(1, am_ref[:, None]))[bad].all())
+    weights = torch.rand(M, device="cuda")
+    (loss * weights).sum().backward()
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().float().requires_grad_(True)
+    (torch.nn.functional.cross_entropy(xr @ wr.t(), targets, reduction="none") * weights).sum().backward()
+    assert _rel_err(x.grad, xr.grad) < 3e-2, _rel_err(x.grad, xr.grad)
+    assert _rel_err(w.grad, wr.grad) < 3e-2, _rel_err(w.grad, wr.grad)
+
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T,cu,heads,kv_heads,d,window", [
+    (1024, [0, 1024], 4, 2, 128, 200),      # window inside one sequence, GQA
+    (1000, [0, 300, 1000], 4, 4, 128, 64),  # packed documents, ragged tail, window smaller than a tile
+    (777, [0, 100, 101, 777], 8, 1, 128, 300),  # MQA, T not a multiple of 64, a one-token document
+    (512, [0, 512], 4, 2, 64, None),        # head dim 64 (zero-padded to the kernel's 128)
+    (640, [0, 256, 640], 2, 2, 96, 100),    # head dim 96 + window
+])
+def test_attention_sm100_windows_and_small_heads(causal, T, cu, heads, kv_heads, d, window):
+    """Sliding windows (as narrowed per-row key bounds), head dims below 128 and GQA/MQA on ragged packed batches,
+    forward and all three gradients, against the dense fp32 expression."""
+    from scaling_b200.ops.attention import attention, attention_dense
+    from scaling_b200.ops.attention_sm100 import sm100_attention_supported
+
+    torch.manual_seed(12)
+    dev = "cuda"
+    q = torch.randn(T, heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(T, kv_heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(T, kv_heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    cu_t = torch.tensor(cu, device=dev, dtype=torch.int32)
+    scale = 1.0 / math.sqrt(d)
+    assert sm100_attention_supported(q, k, v, cu_t, cu_t, causal, window, 0.0)
+    out = attention(q, k, v, cu_t, max(b - a for a, b in zip(cu[:-1], cu[1:])), causal=causal, scale=scale, window=window)
+    qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    ref = attention_dense(qf, kf, vf, cu_t, cu_t, causal, scale, window)
+    assert out.shape == ref.shape
+    assert _rel_err(out, ref) < 2e-2 and _max_rel_per_row(out.flatten(1), ref.flatten(1)) < 6e-2, (
+        _rel_err(out, ref), _max_rel_per_row(out.flatten(1), ref.flatten(1)))
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    ref.backward(dout.float())
+    for name, g, r in (("dq", q.grad, qf.grad), ("dk", k.grad, kf.grad), ("dv", v.grad, vf.grad)):
+        assert _rel_err(g, r) < 3e-2, (name, _rel_err(g, r))
+
+
+@pytest.mark.parametrize("tq,tk,window", [(1, 700, None), (5, 300, None), (1, 129, 64), (130, 1000, None)])
+def test_attention_sm100_kv_cache_decoding(tq, tk, window):
+    """New query tokens against a longer key/value cache (right-aligned causal mask, forward only)."""
+    from scaling_b200.ops.attention import attention, attention_dense
+
+    torch.manual_seed(13)
+    dev = "cuda"
+    q = torch.randn(tq, 8, 128, device=dev, dtype=torch.bfloat16)
+    k = torch.randn(tk, 2, 128, device=dev, dtype=torch.bfloat16)
+    v = torch.randn(tk, 2, 128, device=dev, dtype=torch.bfloat16)
+    cu_q = torch.tensor([0, tq], device=dev, dtype=torch.int32)
+    cu_k = torch.tensor([0, tk], device=dev, dtype=torch.int32)
+    scale = 1.0 / math.sqrt(128)
+    with torch.no_grad():
+        out = attention(q, k, v, cu_q, tq, causal=True, scale=scale, cu_seqlens_k=cu_k, max_seqlen_k=tk, window=window)
+        ref = attention_dense(q.float(), k.float(), v.float(), cu_q, cu_k, True, scale, window)
+    assert _rel_err(out, ref) < 2e-2, _rel_err(out, ref)

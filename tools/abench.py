@@ -39,9 +39,9 @@ for (Tt, heads, kvh, causal) in [(4096, 32, 8, True), (4096, 16, 4, True), (8192
     cu = torch.tensor([0, Tt], device=dev, dtype=torch.int32)
     sc = 128 ** -0.5
     do = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16)
-    ours_f = timeit(lambda: AttentionFn.apply(q, k, v, cu, Tt, causal, sc))
+    ours_f = timeit(lambda: AttentionFn.apply(q, k, v, cu, Tt, causal, sc, None))
     lib_f = timeit(lambda: flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=causal))
-    o1 = AttentionFn.apply(q, k, v, cu, Tt, causal, sc)
+    o1 = AttentionFn.apply(q, k, v, cu, Tt, causal, sc, None)
     o2 = flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=causal)
     err = float((o1.float() - o2.float()).norm() / o2.float().norm())
     ours_b = timeit(lambda: torch.autograd.grad(o1, (q, k, v), do, retain_graph=True))

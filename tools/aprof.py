@@ -17,12 +17,12 @@ for Tt in (4096, 8192):
     cu = torch.tensor([0, Tt], device=dev, dtype=torch.int32)
     do = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16)
     for _ in range(3):
-        o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5)
+        o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5, None)
         torch.autograd.grad(o, (q, k, v), do)
     torch.cuda.synchronize()
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         for _ in range(5):
-            o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5)
+            o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5, None)
             torch.autograd.grad(o, (q, k, v), do)
         torch.cuda.synchronize()
     print("T", Tt)

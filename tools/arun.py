@@ -15,7 +15,7 @@ v = torch.randn(Tt, kvh, 128, device=dev, dtype=torch.bfloat16, requires_grad=Tr
 cu = torch.tensor([0, Tt], device=dev, dtype=torch.int32)
 do = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16)
 for _ in range(2):
-    o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5)
+    o = AttentionFn.apply(q, k, v, cu, Tt, True, 128 ** -0.5, None)
     torch.autograd.grad(o, (q, k, v), do)
 torch.cuda.synchronize()
 print("ok")

@@ -173,9 +173,9 @@ try:
         cu = torch.tensor([0, Tt], device=dev, dtype=torch.int32)
         sc = 128 ** -0.5
         do = torch.randn(Tt, heads, 128, device=dev, dtype=torch.bfloat16)
-        ours_f = timeit(lambda: AttentionFn.apply(q, k, v, cu, Tt, True, sc))
+        ours_f = timeit(lambda: AttentionFn.apply(q, k, v, cu, Tt, True, sc, None))
         lib_f = timeit(lambda: flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=True))
-        o1 = AttentionFn.apply(q, k, v, cu, Tt, True, sc)
+        o1 = AttentionFn.apply(q, k, v, cu, Tt, True, sc, None)
         o2 = flash_attn_varlen_func(q, k, v, cu, cu, Tt, Tt, 0.0, sc, causal=True)
         ours_b = timeit(lambda: torch.autograd.grad(o1, (q, k, v), do, retain_graph=True))
         lib_b = timeit(lambda: torch.autograd.grad(o2, (q, k, v), do, retain_graph=True))

@@ -44,7 +44,7 @@ elif which == "attn":
     cu = torch.tensor([0, T], device=dev, dtype=torch.int32)
 
     def fn():
-        o = AttentionFn.apply(q, k, v, cu, T, True, 128 ** -0.5)
+        o = AttentionFn.apply(q, k, v, cu, T, True, 128 ** -0.5, None)
         torch.autograd.grad(o, (q, k, v), do)
 else:
     raise SystemExit(f"unknown target {which}")

@@ -56,9 +56,9 @@ def config(args, trainer_over: dict) -> dict:
 def run_arm(args) -> None:
     import torch
 
-    port = 29640 + {"reference_init": 0, "reference": 1, "ours": 2}[args.arm]
-    ckpt = WORK / "ckpt"
-    if args.arm == "reference_init":
+    port = 29640 + {"reference_init": 0, "reference": 1, "ours": 2, "ours_init": 3}[args.arm]
+    ckpt = WORK / args.ckpt
+    if args.arm in ("reference_init", "ours_init"):
         over = {"save_dir": str(ckpt), "save_interval": 1, "train_iterations": 1}
     else:
         over = {"load_dir": str(ckpt), "load_optimizer_states": True, "load_context": True, "assert_checkpoint_loaded": True,
@@ -92,7 +92,7 @@ def run_arm(args) -> None:
 
         launch = LaunchConfig(master_port=port, master_addr="127.0.0.1", world_size=1, global_rank=0, local_slot=0, payload=cfg)
         trainer = build_trainer(launch)
-    if args.arm == "reference_init":
+    if args.arm in ("reference_init", "ours_init"):
         # not run_training(): the reference's metric logging divides by a zero peak on GPUs it does not know (B200)
         trainer.train_step()
         trainer.save_checkpoint()
@@ -102,13 +102,16 @@ def run_arm(args) -> None:
         out = trainer.train_step()
         losses.append(float(out.loss))
     torch.cuda.synchronize()
-    json.dump(losses, open(WORK / f"losses_{args.arm}.json", "w"))
+    json.dump(losses, open(WORK / f"losses_{args.arm}_{args.ckpt}.json", "w"))
     print(args.arm, "losses", [round(x, 4) for x in losses[:5]], "...", [round(x, 4) for x in losses[-3:]], flush=True)
 
 
 def main() -> None:
     p = argparse.ArgumentParser()
-    p.add_argument("--arm", default=None, choices=[None, "reference_init", "reference", "ours"])
+    p.add_argument("--arm", default=None, choices=[None, "reference_init", "reference", "ours", "ours_init"])
+    p.add_argument("--ckpt", default="ckpt", help="checkpoint sub-directory under the work dir")
+    p.add_argument("--reverse", action="store_true",
+                   help="the other direction: scaling_b200 writes the checkpoint, the unmodified reference resumes from it")
     p.add_argument("--steps", type=int, default=40)
     p.add_argument("--layers", type=int, default=4)
     p.add_argument("--seqs", type=int, default=4)
@@ -121,8 +124,10 @@ def main() -> None:
 
     shutil.rmtree(WORK, ignore_errors=True)
     write_learnable_dataset(WORK / "data" / "tokens", n_docs=args.seqs * (args.steps + 4), vocab=32000)
-    for arm in ("reference_init", "reference", "ours"):
-        cmd = [sys.executable, __file__, "--arm", arm, "--steps", str(args.steps), "--layers", str(args.layers), "--seqs", str(args.seqs)]
+    ckpt = "ckpt_ours" if args.reverse else "ckpt"
+    for arm in (("ours_init", "reference", "ours") if args.reverse else ("reference_init", "reference", "ours")):
+        cmd = [sys.executable, __file__, "--arm", arm, "--steps", str(args.steps), "--layers", str(args.layers), "--seqs",
+               str(args.seqs), "--ckpt", ckpt]
         env = dict(os.environ)
         if arm.startswith("reference"):
             # environment shim for the torch-2.1-era reference: its torch.load calls predate the weights_only default
@@ -130,12 +135,16 @@ def main() -> None:
         r = subprocess.run(cmd, cwd=str(REPO), env=env, timeout=900)
         if r.returncode != 0:
             raise SystemExit(f"phase {arm} failed with exit code {r.returncode}")
-    ref = json.load(open(WORK / "losses_reference.json"))
-    ours = json.load(open(WORK / "losses_ours.json"))
+    ref = json.load(open(WORK / f"losses_reference_{ckpt}.json"))
+    ours = json.load(open(WORK / f"losses_ours_{ckpt}.json"))
     rel = [abs(a - b) / abs(a) for a, b in zip(ref, ours)]
     result = {"config": f"mistral-7b geometry, {args.layers} layers, seq {SEQ}, {args.seqs} sequences/step, bf16, lr 1e-4 (10 warm-up steps, cosine)",
-              "protocol": "reference trains 1 step and saves; both frameworks resume from that checkpoint (weights, "
-                          "optimizer state, data position) and train the same steps",
+              "protocol": ("scaling_b200 trains 1 step and saves; the UNMODIFIED reference and scaling_b200 both resume from "
+                           "that checkpoint (weights, optimizer state, data position) and train the same steps"
+                           if args.reverse else
+                           "reference trains 1 step and saves; both frameworks resume from that checkpoint (weights, "
+                           "optimizer state, data position) and train the same steps"),
+              "checkpoint_written_by": "scaling_b200" if args.reverse else "reference",
               "steps": args.steps, "reference": ref, "scaling_b200": ours, "relative_difference": rel,
               "max_relative_difference": max(rel), "first_step_relative_difference": rel[0],
               "mean_relative_difference_last_10": sum(rel[-10:]) / len(rel[-10:])}
