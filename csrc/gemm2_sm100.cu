@@ -71,6 +71,10 @@ struct Params {
   // [r·rs_seq_per_rank, (r+1)·rs_seq_per_rank) of every batch item (Megatron sequence parallelism).  A 256-row tile lies
   // inside one rank's range; it is pushed to and reduced by that owner only, and D is the owner's compact [b·s/tp, N].
   int rs_seq, rs_seq_per_rank;
+  // two-shot all-reduce (tp > 2): tile t is reduced by rank t % tp only — partials travel to that owner, the owner's
+  // reducers store the final bf16 tile into slot `owner` of every other rank's workspace (unused there: the owner never
+  // sends a partial of its own tiles) and the other ranks copy it out.  (tp - 1) / tp of the one-shot bytes per phase.
+  int two_shot;
   unsigned long long* prof;       // optional [grid][8] globaltimer stamps of the phases (sb_gemm2_set_profile_buffer)
   uint32_t flag_slot;             // u32 flags per sender slot
   unsigned long long slot_bytes;  // bytes per sender slot
@@ -221,6 +225,14 @@ SB_DEVICE int rs_owner(const Params& p, int row0) { return (row0 % p.rs_seq) / p
 SB_DEVICE int rs_out_row(const Params& p, int row) {
   const int b = row / p.rs_seq, s = row % p.rs_seq;
   return b * p.rs_seq_per_rank + s % p.rs_seq_per_rank;
+}
+
+// Which rank reduces tile t (first row tm * BM): the sequence owner in reduce-scatter mode, t % tp in two-shot mode,
+// -1 = every rank (one-shot all-reduce).
+SB_DEVICE int tile_owner(const Params& p, int t, int tm) {
+  if (p.rs_seq > 0) return rs_owner(p, tm * BM);
+  if (p.two_shot) return t % p.tp_size;
+  return -1;
 }
 
 // Work unit u of the persistent schedule -> (tile, k-block range, part index or -1 when the tile is not split).
@@ -415,10 +427,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         done += 4;
         while (ld_acquire_cta_smem(&bars->pushed) < done) __nanosleep(40);
         fence_acq_rel_sys();  // the four warps' bulk copies (completed, observed through `pushed`) before the flags
-        if (p.rs_seq > 0) {
-          int tm_, tn_;
-          tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
-          st_relaxed_sys(p.ar_flags[rs_owner(p, tm_ * BM)] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
+        int tm_, tn_;
+        tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
+        const int owner = tile_owner(p, t, tm_);
+        if (owner >= 0) {
+          st_relaxed_sys(p.ar_flags[owner] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
         } else {
           for (int r = 0; r < p.tp_size; ++r)
             st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
@@ -438,16 +451,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       int tm, tn;
       tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
       const uint32_t ct = (uint32_t)t * 2 + rank;
-      if (p.rs_seq > 0 && rs_owner(p, tm * BM) != p.tp_rank) continue;  // another rank reduces this tile
+      const int owner = tile_owner(p, t, tm);
+      if (p.rs_seq > 0 && owner != p.tp_rank) continue;  // another rank reduces this tile and keeps the result
+      // two-shot, somebody else's tile: wait for the owner's FINAL tile in slot `owner` and copy it out
+      const bool copy_only = p.two_shot && owner != p.tp_rank;
+      const bool spread = p.two_shot && owner == p.tp_rank;  // owner: also store the result into the peers' slots
+      const int src0 = copy_only ? owner : 0, nsrc = copy_only ? 1 : p.tp_size;
       if (lane == 0) {
-        for (int s = 0; s < p.tp_size; ++s) wait_flag(myflags + (size_t)s * p.flag_slot + ct, p.epoch);
+        for (int s = 0; s < nsrc; ++s) wait_flag(myflags + (size_t)(src0 + s) * p.flag_slot + ct, p.epoch);
         if (rw == 0) {
           if (t == cluster_id) prof_stamp(p.prof, 4);
           if (t + num_clusters >= num_tiles) prof_stamp(p.prof, 5);
         }
       }
       __syncwarp();
-      const uint8_t* base = mine + ((size_t)ct * 4 + slab) * kSlabBytes;
+      const size_t slab_off = ((size_t)ct * 4 + slab) * kSlabBytes;
+      const uint8_t* base = mine + (size_t)src0 * p.slot_bytes + slab_off;
       const int row0 = tm * BM + rank * 128 + slab * 32;
       const int n0 = tn * BN;
 #pragma unroll 1
@@ -457,7 +476,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         for (int it = 0; it < 8; ++it) {
           const size_t off = (size_t)c4 * kChunkBytes + (size_t)(lane + 32 * it) * 16;
           xa[it] = ld_cg_v4(base + off);
-          xb[it] = ld_cg_v4(base + p.slot_bytes + off);
+          xb[it] = nsrc > 1 ? ld_cg_v4(base + p.slot_bytes + off) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -465,7 +484,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           acc_bf16x8(f, xa[it]);
           acc_bf16x8(f, xb[it]);
           const size_t off = (size_t)c4 * kChunkBytes + (size_t)(lane + 32 * it) * 16;
-          for (int s = 2; s < p.tp_size; ++s) acc_bf16x8(f, ld_cg_v4(base + (size_t)s * p.slot_bytes + off));
+          for (int s = 2; s < nsrc; ++s) acc_bf16x8(f, ld_cg_v4(base + (size_t)s * p.slot_bytes + off));
           const int r_in = (lane >> 3) + 4 * it;
           const int j = (lane & 7) ^ (r_in & 7);
           const int row = row0 + r_in;
@@ -473,17 +492,33 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           if (row >= p.M || col >= p.N) continue;
           const int drow = p.rs_seq > 0 ? rs_out_row(p, row) : row;
           __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)drow * p.ldd + col;
+          const bool add_bias = bias && !copy_only;  // a copied tile already carries the bias
           if (col + 8 <= p.N) {
-            if (bias) {
+            if (add_bias) {
               const uint4 bv = *reinterpret_cast<const uint4*>(bias + col);
               acc_bf16x8(f, bv);
             }
-            *reinterpret_cast<uint4*>(dst) =
+            const uint4 o =
                 make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+            *reinterpret_cast<uint4*>(dst) = o;
+            if (spread) {
+              for (int r = 0; r < p.tp_size; ++r)
+                if (r != p.tp_rank)
+                  *reinterpret_cast<uint4*>(p.ar_data[r] + (size_t)p.tp_rank * p.slot_bytes + slab_off + off) = o;
+            }
           } else {
             for (int i = 0; i < 8 && col + i < p.N; ++i)
-              dst[i] = __float2bfloat16(f[i] + (bias ? __bfloat162float(bias[col + i]) : 0.f));
+              dst[i] = __float2bfloat16(f[i] + (add_bias ? __bfloat162float(bias[col + i]) : 0.f));
           }
+        }
+      }
+      if (spread) {
+        // all eight reducer warps have stored the final tile into the peers' slots: publish "final ready"
+        asm volatile("bar.sync 2, 256;\n" ::: "memory");
+        if (rw == 0 && lane == 0) {
+          fence_acq_rel_sys();
+          for (int r = 0; r < p.tp_size; ++r)
+            if (r != p.tp_rank) st_relaxed_sys(p.ar_flags[r] + (size_t)p.tp_rank * p.flag_slot + ct, p.epoch);
         }
       }
     }
@@ -502,11 +537,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       if (ew == 0 && lane == 0 && t + num_clusters >= num_tiles) prof_stamp(p.prof, 1);
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
       const size_t slab_off = (size_t)p.tp_rank * p.slot_bytes + ((size_t)ct * 4 + ew) * kSlabBytes;
-      int rs_tile_owner = 0;
-      if (p.rs_seq > 0) {
+      int push_owner;
+      {
         int tm_, tn_;
         tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
-        rs_tile_owner = rs_owner(p, tm_ * BM);
+        push_owner = tile_owner(p, t, tm_);
       }
       if (lane == 0) bulk_wait_read<0>();  // the previous tile's copies have drained the slab buffer
       __syncwarp();
@@ -537,8 +572,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) {
         // ONE 16 KiB bulk copy per destination: the slab is contiguous in the workspace and in shared memory
-        if (p.rs_seq > 0) {
-          bulk_store_s2g(p.ar_data[rs_tile_owner] + slab_off, slab_buf, kSlabBytes);
+        if (push_owner >= 0) {
+          bulk_store_s2g(p.ar_data[push_owner] + slab_off, slab_buf, kSlabBytes);
         } else {
           for (int r = 0; r < p.tp_size; ++r) bulk_store_s2g(p.ar_data[r] + slab_off, slab_buf, kSlabBytes);
         }
@@ -1045,6 +1080,12 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
                                  const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
                                  unsigned long long slot_bytes, unsigned int flag_slot, int rs_seq, int max_ctas,
                                  cudaStream_t stream, const LowRank* lr = nullptr) {
+  // one-shot (every rank reduces every tile) is byte-optimal only for two ranks; beyond that tiles have owners
+  static int force_two_shot = -1;
+  if (force_two_shot < 0) {
+    const char* e = getenv("SCALING_B200_AR_TWO_SHOT");
+    force_two_shot = e ? atoi(e) : 2;  // 0 never, 1 always, 2 (default) when tp > 2
+  }
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if (tp_size < 2 || tp_size > kMaxTP || tp_rank < 0 || tp_rank >= tp_size) return -20;
   Params p{};
@@ -1061,6 +1102,7 @@ static int fused_collective_impl(const void* A, const void* B, void* D, const vo
     p.prof = g_prof_buf[dev & 63];
   }
   p.rs_seq = rs_seq, p.rs_seq_per_rank = rs_seq > 0 ? rs_seq / tp_size : 0;
+  p.two_shot = (rs_seq == 0 && (force_two_shot == 1 || (force_two_shot == 2 && tp_size > 2))) ? 1 : 0;
   p.tp_rank = tp_rank, p.tp_size = tp_size, p.epoch = epoch, p.flag_slot = flag_slot, p.slot_bytes = slot_bytes;
   for (int r = 0; r < tp_size; ++r) {
     p.ar_data[r] = reinterpret_cast<uint8_t*>(data_ptrs[r]);

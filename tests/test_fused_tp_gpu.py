@@ -11,7 +11,11 @@ from tests.utils import dist_launcher
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")]
 
 
-def _kernel_worker(rank: int, world_size: int, master_port: int):
+def _kernel_worker(rank: int, world_size: int, master_port: int, two_shot: bool = False):
+    if two_shot:  # read once by the library: force the owner-reduces / final-tile-broadcast protocol also at tp = 2
+        import os
+
+        os.environ["SCALING_B200_AR_TWO_SHOT"] = "1"
     import torch.distributed as dist
 
     from scaling_b200.ops import kernels as K
@@ -144,6 +148,13 @@ def test_gemm_allreduce_kernel(world):
         pytest.skip(f"needs {world} GPUs")
     res = dist_launcher(_kernel_worker, world_size=world, timeout=300)
     assert len(res) == world and all(v < 2e-2 for v in res.values())
+
+
+def test_gemm_allreduce_two_shot_protocol_on_two_ranks():
+    """The tp > 2 protocol (partials to the tile's owner, owner stores the final tile into the peers' slots, peers copy it
+    out) forced on two ranks, so that it is covered wherever two GPUs are."""
+    res = dist_launcher(_kernel_worker, world_size=2, timeout=300, two_shot=True)
+    assert len(res) == 2 and all(v < 2e-2 for v in res.values())
 
 
 def _train_worker(rank: int, world_size: int, master_port: int, config_dict, fused: bool):
@@ -323,10 +334,11 @@ def test_lora_fused_projections_match_separate_lora_linears(tmp_path, mp):
     a = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
          "sequence_length": 256, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"},
          "lora_config": {"name": "lo", "rank": 16, "alpha": 32}}
-    cfg = tiny_config(prefix, mp=mp, iters=6, gas=2, arch=a)
+    cfg = tiny_config(prefix, mp=mp, iters=6, gas=2, arch=a,
+                      learning_rate_scheduler={"learning_rate": 0.002, "learning_rate_decay_style": "constant"})
     fused = dist_launcher(_lora_worker, world_size=mp, timeout=400, config_dict=cfg, fused=True)[0]
     plain = dist_launcher(_lora_worker, world_size=mp, timeout=400, config_dict=cfg, fused=False)[0]
-    assert len(fused) == 6 and all(x == x for x in fused) and fused[-1] < fused[0]
+    assert len(fused) == 6 and all(x == x for x in fused) and fused[-1] < fused[0], (fused, plain)
     for x, y in zip(fused, plain):
         assert abs(x - y) / abs(y) < 2e-2, (fused, plain)
 

@@ -70,6 +70,17 @@ shapes = [
     ("mlp_up_wgrad_fp32acc", 28672, 4096, T, True, True, torch.float32, True),
     ("mlp_down_wgrad_fp32acc", 4096, 14336, T, True, True, torch.float32, True),
     ("square_8192", 8192, 8192, 8192, False, False, torch.bfloat16, False),
+    # per-rank shapes at tensor parallel 2 (N or K halved)
+    ("tp2_qkv_fprop", T, 3072, 4096, False, False, torch.bfloat16, False),
+    ("tp2_attn_out_fprop", T, 4096, 2048, False, False, torch.bfloat16, False),
+    ("tp2_mlp_down_fprop", T, 4096, 7168, False, False, torch.bfloat16, False),
+    ("tp2_lm_head_fprop", T, 16000, 4096, False, False, torch.bfloat16, False),
+    ("tp2_qkv_dgrad", T, 4096, 3072, False, True, torch.bfloat16, False),
+    ("tp2_mlp_up_dgrad", T, 4096, 14336, False, True, torch.bfloat16, False),
+    ("tp2_mlp_down_dgrad", T, 7168, 4096, False, True, torch.bfloat16, False),
+    ("tp2_qkv_wgrad_fp32acc", 3072, 4096, T, True, True, torch.float32, True),
+    ("tp2_mlp_up_wgrad_fp32acc", 14336, 4096, T, True, True, torch.float32, True),
+    ("tp2_mlp_down_wgrad_fp32acc", 4096, 7168, T, True, True, torch.float32, True),
 ]
 for s in shapes:
     try:
@@ -153,6 +164,61 @@ def lib_adam():
 
 ref = timeit(lib_adam, iters=5)
 r = {"name": "adamw_256M", "ours_ms": ours, "lib_ms": ref, "gbs": n * (4 * 3 * 2 + 2 + 2) / ours / 1e6, "speedup_vs_lib": ref / ours}
+print(r, flush=True)
+res["fused"].append(r)
+
+# LM head with the CE statistics in the GEMM epilogue (+ combine / finalize) vs plain GEMM + the separate stats kernel
+xh = torch.randn(T, 4096, device=dev, dtype=torch.bfloat16)
+wh = torch.randn(32000, 4096, device=dev, dtype=torch.bfloat16) / 64
+
+
+def fused_head():
+    lg, part = K.gemm_xent_stats(xh, wh)
+    return K.xent_from_partials(part, lg, tg, 0)
+
+
+def unfused_head():
+    lg = K.gemm(xh, wh)
+    return K.xent_stats(lg, tg, 0)
+
+
+ours = timeit(fused_head)
+ref = timeit(unfused_head)
+
+
+def lib_head():
+    return torch.nn.functional.cross_entropy((xh @ wh.t()).float(), tg, reduction="none")
+
+
+lib = timeit(lib_head)
+r = {"name": "lm_head_plus_ce_forward_4096x32000x4096", "epilogue_stats_ms": ours, "gemm_plus_stats_kernel_ms": ref,
+     "cublas_plus_aten_ce_ms": lib, "speedup_vs_unfused": ref / ours, "speedup_vs_lib": lib / ours}
+print(r, flush=True)
+res["fused"].append(r)
+
+# LoRA: low-rank pair as extra K-slab vs base GEMM + two small GEMMs + add (rank 64, q-projection shape)
+xl = torch.randn(T, 4096, device=dev, dtype=torch.bfloat16)
+wl = torch.randn(4096, 4096, device=dev, dtype=torch.bfloat16) / 64
+al = torch.randn(64, 4096, device=dev, dtype=torch.bfloat16) / 64
+bl = torch.randn(4096, 64, device=dev, dtype=torch.bfloat16) / 8
+
+
+def lora_fused():
+    t = K.gemm(xl, al)
+    return K.gemm_lowrank(xl, wl, t, bl)
+
+
+def lora_unfused():
+    return K.gemm(xl, wl) + K.gemm(K.gemm(xl, al), bl)
+
+
+def lora_lib():
+    return xl @ wl.t() + (xl @ al.t()) @ bl.t()
+
+
+ours, ref, lib = timeit(lora_fused), timeit(lora_unfused), timeit(lora_lib)
+r = {"name": "lora_q_proj_rank64_4096x4096x4096", "fused_ms": ours, "own_gemms_plus_add_ms": ref, "cublas_plus_add_ms": lib,
+     "speedup_vs_unfused": ref / ours, "speedup_vs_lib": lib / ours}
 print(r, flush=True)
 res["fused"].append(r)
 
