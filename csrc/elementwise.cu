@@ -470,6 +470,35 @@ __global__ void sum_slots_kernel(const uint4* __restrict__ slots, uint4* __restr
     out[i] = make_uint4(sb::pack_bf16(f[0], f[1]), sb::pack_bf16(f[2], f[3]), sb::pack_bf16(f[4], f[5]), sb::pack_bf16(f[6], f[7]));
   }
 }
+// gather_push with arrival counters (feeds the gated GEMM): one CTA copies one chunk of kGateChunkRows rows
+// of the local shard to every rank, then adds 1 (release, system scope) to the counter of the 256-row tile the chunk
+// belongs to on every rank.  A complete tile therefore shows (256 / kGateChunkRows) * calls on that buffer.
+constexpr int kGateChunkRows = 8;
+struct GatePeers {
+  unsigned int* p[8];
+};
+__global__ void seq_gather_push_counted_kernel(const uint4* __restrict__ src, EmbPeers outs, GatePeers gates, int rank,
+                                               int s_local, int vec_per_row, int n_chunks) {
+  const int tp = outs.n;
+  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+    const size_t row_first = (size_t)chunk * kGateChunkRows;
+    const size_t b = row_first / s_local, sl0 = row_first % s_local;
+    const size_t drow0 = b * ((size_t)s_local * tp) + (size_t)rank * s_local + sl0;  // chunks never straddle a batch item
+    const size_t n_vec = (size_t)kGateChunkRows * vec_per_row;
+    for (size_t i = threadIdx.x; i < n_vec; i += blockDim.x) {
+      const uint4 v = src[row_first * vec_per_row + i];
+      for (int r = 0; r < tp; ++r) reinterpret_cast<uint4*>(outs.p[r])[drow0 * vec_per_row + i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned int tile = (unsigned int)(drow0 / 256);
+      for (int r = 0; r < tp; ++r)
+        asm volatile("red.release.sys.global.add.u32 [%0], 1;\n" ::"l"(gates.p[r] + tile) : "memory");
+    }
+    __syncthreads();
+  }
+}
 static int fill_peers(EmbPeers& o, const unsigned long long* ptrs, int tp) {
   if (tp < 1 || tp > 8) return -1;
   o.n = tp;
@@ -485,6 +514,24 @@ extern "C" int sb_seq_gather_push(const void* src, const unsigned long long* out
   if (fill_peers(o, out_ptrs, tp)) return -5;
   const size_t total = (size_t)batch * s_local * (hidden / 8);
   seq_gather_push_kernel<<<blocks_for(total), 256, 0, st>>>((const uint4*)src, o, rank, s_local, hidden / 8, total);
+  return (int)cudaGetLastError();
+}
+// As sb_seq_gather_push, plus arrival counters: gate_ptrs are the tp peer-mapped u32 counter arrays (one counter per
+// 256-row tile of the [batch * s_local * tp, hidden] gather buffer).  Requires s_local % 256 == 0.  After n calls on a
+// buffer every counter of a complete tile reads n * sb_seq_gather_chunks_per_tile().
+extern "C" int sb_seq_gather_chunks_per_tile() { return 256 / kGateChunkRows; }
+extern "C" int sb_seq_gather_push_counted(const void* src, const unsigned long long* out_ptrs,
+                                          const unsigned long long* gate_ptrs, int tp, int rank, int batch, int s_local,
+                                          int hidden, cudaStream_t st) {
+  if (batch <= 0 || s_local <= 0) return 0;
+  if (hidden % 8 || s_local % 256) return -1;
+  EmbPeers o{};
+  if (fill_peers(o, out_ptrs, tp)) return -5;
+  GatePeers g{};
+  for (int r = 0; r < tp; ++r) g.p[r] = reinterpret_cast<unsigned int*>(gate_ptrs[r]);
+  const int n_chunks = batch * s_local / kGateChunkRows;
+  const int grid = n_chunks < 148 * 8 ? n_chunks : 148 * 8;
+  seq_gather_push_counted_kernel<<<grid, 256, 0, st>>>((const uint4*)src, o, g, rank, s_local, hidden / 8, n_chunks);
   return (int)cudaGetLastError();
 }
 // src: [batch, s_local * tp, hidden] bf16 partial sums; out_ptrs: tp peer-mapped [tp, batch, s_local, hidden] slot buffers

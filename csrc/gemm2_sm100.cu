@@ -42,11 +42,12 @@ enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, 
 // tiles i+1.., the reduction of tile i overlaps both.
 constexpr int kMaxTP = 8;
 constexpr int kArThreads = 512;                          // 4 control + 4 epilogue + 8 reducer warps
-constexpr int kArStages = 5;                             // one TMA stage less than the plain kernel: room for the slabs
+constexpr int kArStages = 6;                             // same TMA ring depth as the plain kernel
 constexpr uint32_t kChunkBytes = 32 * 64 * 2;            // one sub-tile: 32 rows x 64 bf16
 constexpr uint32_t kSlabBytes = 4 * kChunkBytes;         // one epilogue warp's 32 x 256 slab
 constexpr uint32_t kCtaTileBytes = 4 * kSlabBytes;       // 128 x 256 bf16
-constexpr uint32_t kStagingBytes = 4 * kSlabBytes;       // every epilogue warp stages its whole slab (64 KiB per CTA)
+constexpr uint32_t kHalfSlabBytes = 2 * kChunkBytes;     // 32 rows x 128 columns: what one epilogue warp stages at a time
+constexpr uint32_t kStagingBytes = 4 * kHalfSlabBytes;   // 32 KiB per CTA (a full slab per warp would cost a TMA stage)
 constexpr uint32_t kArSmemBytes = kArStages * (128 * BK * 2 * 2) + 256 + kStagingBytes + 1024;
 
 struct Params {
@@ -59,6 +60,11 @@ struct Params {
   int swiglu_up_row_offset;
   int tiles_m, tiles_n;
   int kb_extra;  // k-blocks of the low-rank slab behind the main K range (0 = none)
+  // all-gather -> GEMM: rows of A arrive from tensor-parallel peers (NVLink stores into this GPU's gather
+  // buffer); gate[tm] counts the arrived row chunks of 256-row tile tm.  The TMA producer starts a tile only once
+  // gate[tm] has reached gate_target, so tiles of the local shard start at once and remote tiles as they land.
+  const uint32_t* gate;
+  uint32_t gate_target;
   // split-K tail: the last, partial wave of tiles is cut along K into `split` parts so that it fills the machine
   int full_tiles;   // tiles [0, full_tiles) run whole; the remaining `num_tiles - full_tiles` are split
   int split;        // parts per tail tile (1 = no splitting)
@@ -349,6 +355,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         const Unit w = get_unit(u, p, k_blocks);
         int tm, tn;
         tile_coords(w.tile, p.tiles_m, p.tiles_n, tm, tn);
+        if (p.gate) {
+          // acquire the peers' (generic-proxy) stores of this row tile, then order them before the async-proxy TMA reads
+          const uint32_t* g = p.gate + tm;
+          const unsigned long long t0 = global_timer_ns();
+          int spins = 0;
+          while ((int)(ld_acquire_sys(g) - p.gate_target) < 0) {
+            if (++spins > 16) {
+              __nanosleep(64);
+              if ((spins & 1023) == 0 && global_timer_ns() - t0 > 30000000000ull) __trap();
+            }
+          }
+          asm volatile("fence.proxy.async.global;\n" ::: "memory");
+        }
         const int m0 = tm * BM + rank * 128;
         const int nb = (kEpi == kSwiGLU) ? tn * (BN / 2) + (rank ? p.swiglu_up_row_offset : 0) : tn * BN + rank * 128;
         for (int kb = w.kb0; kb < w.kb1; ++kb) {
@@ -526,7 +545,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   } else if (kEpi == kAllReduce && warp >= 4) {
     // ===================== epilogue (kAllReduce): push bf16 partial tiles into every rank's workspace =====================
     const int ew = warp & 3;
-    uint8_t* slab_buf = smem + kNumStages * kStageBytes + 256 + (uint32_t)ew * kSlabBytes;
+    uint8_t* half_buf = smem + kNumStages * kStageBytes + 256 + (uint32_t)ew * kHalfSlabBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
     int pending_ct = -1;
@@ -543,43 +562,51 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         tile_coords(t, p.tiles_m, p.tiles_n, tm_, tn_);
         push_owner = tile_owner(p, t, tm_);
       }
-      if (lane == 0) bulk_wait_read<0>();  // the previous tile's copies have drained the slab buffer
-      __syncwarp();
+      // the slab travels as two 8 KiB halves (two 64-column chunks each) through one staging buffer per warp
 #pragma unroll 1
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint8_t* buf = slab_buf + c4 * kChunkBytes;
+      for (int hs = 0; hs < 2; ++hs) {
+        if (lane == 0) bulk_wait_read<0>();  // the previous half's copies have drained the staging buffer
+        __syncwarp();
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c4 = 2 * hs + cc;
+          uint8_t* buf = half_buf + cc * kChunkBytes;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(taddr + c4 * 64 + h * 32, v);
-          tmem_ld_wait();
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(taddr + c4 * 64 + h * 32, v);
+            tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint4 o = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
-                                       pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
-                                       pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
-                                       pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
-            const int pos = (h * 4 + i) ^ (lane & 7);  // 16-byte unit swizzle: conflict-free staging stores
-            *reinterpret_cast<uint4*>(buf + lane * 128 + pos * 16) = o;
+            for (int i = 0; i < 4; ++i) {
+              const uint4 o = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                                         pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                                         pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                                         pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
+              const int pos = (h * 4 + i) ^ (lane & 7);  // 16-byte unit swizzle: conflict-free staging stores
+              *reinterpret_cast<uint4*>(buf + lane * 128 + pos * 16) = o;
+            }
           }
         }
-      }
-      // accumulator fully read: hand the TMEM stage back before the pushes
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        // ONE 16 KiB bulk copy per destination: the slab is contiguous in the workspace and in shared memory
-        if (push_owner >= 0) {
-          bulk_store_s2g(p.ar_data[push_owner] + slab_off, slab_buf, kSlabBytes);
-        } else {
-          for (int r = 0; r < p.tp_size; ++r) bulk_store_s2g(p.ar_data[r] + slab_off, slab_buf, kSlabBytes);
+        if (hs == 1) {  // accumulator fully read: hand the TMEM stage back before the last pushes
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(&bars->acc_empty[acc], 0);
         }
-        bulk_commit();
-        if (pending_ct >= 0) {  // the previous tile's group has completed: hand it to the signal warp
-          bulk_wait<1>();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          const size_t off = slab_off + (size_t)hs * kHalfSlabBytes;
+          if (push_owner >= 0) {
+            bulk_store_s2g(p.ar_data[push_owner] + off, half_buf, kHalfSlabBytes);
+          } else {
+            for (int r = 0; r < p.tp_size; ++r) bulk_store_s2g(p.ar_data[r] + off, half_buf, kHalfSlabBytes);
+          }
+          bulk_commit();
+        }
+      }
+      if (lane == 0) {
+        if (pending_ct >= 0) {  // the previous tile's two groups have completed: hand it to the signal warp
+          bulk_wait<2>();
           red_release_cta_smem_inc(&bars->pushed);
         }
         pending_ct = (int)ct;
@@ -920,9 +947,23 @@ static int make_maps(Maps& m, const void* A, const void* B, int M, int N, int K,
   return 0;
 }
 
+// Arrival gate of the NEXT 2-CTA GEMM launched on the current device (consumed by that launch): see Params::gate.
+struct PendingGate {
+  const uint32_t* gate = nullptr;
+  uint32_t target = 0;
+};
+static PendingGate g_pending_gate[64];
+
 template <int AM, int BMj, int EPI, typename OutT>
 static int launch(const Maps& m, Params& p, cudaStream_t stream, int max_ctas) {
   auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
+  {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    PendingGate& pg = g_pending_gate[dev & 63];
+    p.gate = pg.gate, p.gate_target = pg.target;
+    pg.gate = nullptr;
+  }
   static PerDeviceOnce once;  // the attribute is per device
   if (once.first())
     SB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1005,6 +1046,17 @@ static int gemm2_impl(const void* A, const void* B, void* D, const void* bias, i
   SB_DISPATCH(1, 0)
 #undef SB_DISPATCH
   return -10;
+}
+
+// all-gather -> GEMM gate for the NEXT sb_gemm2_* launch on the current device (any epilogue): `gate` is a device array
+// with one u32 arrival counter per 256-row tile of A, `target` the value a complete tile shows (see
+// sb_seq_gather_push_counted in elementwise.cu).  One-shot: the launch clears it.  A must be row-major ([M, K]).
+extern "C" int sb_gemm2_set_gate(const unsigned int* gate, unsigned int target) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  g_pending_gate[dev & 63].gate = gate;
+  g_pending_gate[dev & 63].target = target;
+  return 0;
 }
 
 // Same contract as sb_gemm_bf16 (gemm_sm100.cu), computed by CTA pairs (cta_group::2).

@@ -58,6 +58,63 @@ int sb_gemm2_reduce_scatter_bf16(const void* A, const void* B, void* D, const vo
                                  const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
                                  unsigned long long slot_bytes, unsigned int flag_slot, int seq, int max_ctas,
                                  cudaStream_t st);
+/* LoRA-fused linear: D (+)= A·Bᵀ + A2·B2ᵀ in one accumulator; the low-rank pair (A2 [M,K2]; B2 [N,K2] or,
+ * with b_layout 1, [K2,N]) rides as extra k-blocks behind the main K range.  K2 % 8 == 0.  The _allreduce_ form sums the
+ * result over the TP group in the same launch.  Reference: extra F.linear calls + add (core/nn/lora.py:103-112) and an
+ * all-gather of the attention output for the dense projection (core/nn/attention/attention.py:690-701). */
+int sb_gemm2_lowrank_bf16(const void* A, const void* B, const void* A2, const void* B2, void* D, const void* bias, int M,
+                          int N, int K, int K2, int lda, int ldb, int lda2, int ldb2, int ldd, int b_layout, int out_dtype,
+                          int epilogue, int max_ctas, cudaStream_t st);
+int sb_gemm2_allreduce_lowrank_bf16(const void* A, const void* B, const void* A2, const void* B2, void* D,
+                                    const void* bias, int M, int N, int K, int K2, int lda, int ldb, int lda2, int ldb2,
+                                    int ldd, int b_layout, const unsigned long long* data_ptrs,
+                                    const unsigned long long* flag_ptrs, int tp_rank, int tp_size, unsigned int epoch,
+                                    unsigned long long slot_bytes, unsigned int flag_slot, int max_ctas, cudaStream_t st);
+/* LM-head GEMM with the cross-entropy statistics in its epilogue: logits [M,N] bf16 and stats
+ * [M, sb_gemm2_xent_tiles(N)] float4 = (max, Σexp(x − max), unused, arg-max column as int bits) per 256-column tile.
+ * Reference: F.linear + all-gather + fp32 copy + cross_entropy (lm_head_tied.py:41-43, model.py:56-76). */
+long long sb_gemm2_xent_tiles(int N);
+int sb_gemm2_xent_stats_bf16(const void* X, const void* W, void* logits, float* stats, int M, int N, int K, int ldx,
+                             int ldw, int ldl, int max_ctas, cudaStream_t st);
+/* all-gather -> GEMM: arrival gate for the NEXT sb_gemm2_* launch on the current device.  gate[tm] counts
+ * the row chunks of A's 256-row tile tm that have arrived from the TP peers (sb_seq_gather_push_counted); the TMA
+ * producer starts a tile when gate[tm] >= target.  One-shot.  Reference: all_gather_into_tensor before F.linear
+ * (core/nn/linear/utils.py:305, core/nn/norm/rms_norm.py:57-61). */
+int sb_gemm2_set_gate(const unsigned int* gate, unsigned int target);
+/* Optional phase profile of the fused collective kernels: caller-owned buffer of grid x 8 u64 %globaltimer stamps for
+ * the current device (NULL = off).  No reference counterpart. */
+int sb_gemm2_set_profile_buffer(unsigned long long* buf);
+
+/* ---- peer-memory runtime and collectives issued by this library's own kernels (csrc/runtime.cu, elementwise.cu,
+ *      optim.cu) — SURVEY §8 C1 / E1 / O2 / G2.  All pointer arrays are host arrays of peer-mapped addresses in rank
+ *      order (own rank included). ---- */
+/* Device-side barrier over <= 8 GPUs: flag_ptrs[r] = rank r's u32[world] flag array; epoch grows by 1 per barrier. */
+int sb_device_barrier(const unsigned long long* flag_ptrs, int rank, int world, unsigned int epoch, cudaStream_t st);
+/* Data-parallel gradient all-reduce without ZeRO: this rank sums ITS chunk of every arena and stores the sum into every
+ * arena (reference core/optimizer/allreduce.py:16-22). */
+int sb_dp_allreduce(const unsigned long long* peer_chunks, int n_peers, long long n, int grad_dtype, cudaStream_t st);
+/* Vocab-parallel embedding reduced by placement: the rank owning a token's row stores it into every rank's output (seq ==
+ * 0) or into the output of the rank owning the token's sequence position (seq > 0: sequence-parallel scatter); no dense
+ * all-reduce (reference core/nn/linear/vocab_parallel_embedding.py:122-140). */
+int sb_embedding_fwd_peers(const long long* ids, const void* W, const unsigned long long* out_ptrs, int tp, int tokens,
+                           int hidden, long long vocab_start, long long vocab_end, int seq, cudaStream_t st);
+/* Sequence-parallel all-gather / reduce-scatter by peer stores (reference core/nn/linear/utils.py:279-305); follow each
+ * with sb_device_barrier, except the _counted gather whose consumer is a gated GEMM (sb_gemm2_set_gate). */
+int sb_seq_gather_push(const void* src, const unsigned long long* out_ptrs, int tp, int rank, int batch, int s_local,
+                       int hidden, cudaStream_t st);
+int sb_seq_gather_chunks_per_tile(void);
+int sb_seq_gather_push_counted(const void* src, const unsigned long long* out_ptrs, const unsigned long long* gate_ptrs,
+                               int tp, int rank, int batch, int s_local, int hidden, cudaStream_t st);
+int sb_seq_scatter_push(const void* src, const unsigned long long* out_ptrs, int tp, int rank, int batch, int s_local,
+                        int hidden, cudaStream_t st);
+int sb_sum_slots(const void* slots, void* out, int tp, long long n, cudaStream_t st);
+/* Cross-entropy from the LM-head epilogue statistics: merge the tiles, pick the target logit, exchange 16 bytes per
+ * token across the TP group (peer stores), then — after a barrier — loss / lse / arg-max per token. */
+int sb_xent_combine(const float* partial, int tiles, const void* logits, long long ld, const long long* targets,
+                    int tokens, int vocab_local, long long vocab_start, const unsigned long long* out_ptrs, int tp,
+                    int rank, cudaStream_t st);
+int sb_xent_finalize(const float* all, int tp, int tokens, float* loss, float* lse, long long* argmax, cudaStream_t st);
+
 /* Fused ZeRO-1 step over data-parallel peer memory (csrc/optim.cu): reduce-scatter as peer loads, all-gather as peer
  * stores inside AdamW.  Reference counterpart: all-reduce + slice, AdamW, all_gather (parameter_group.py:346-481). */
 int sb_zero_reduce(const unsigned long long* peer_grads, int n_peers, void* own, long long n, int grad_dtype,
@@ -80,12 +137,24 @@ int sb_qkv_rope(const unsigned long long* ins, const unsigned long long* outs, c
 int sb_attention_fwd(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                      const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                      long long v_pitch, float scale, int causal, cudaStream_t st);
+/* Generalised key side: k, v hold Tk rows (KV-cache decoding, Tk != T needs causal == 0) and with causal == 0 the arrays
+ * are per-row KEY bounds "row t attends to keys [seg_start[t], seg_end[t])", non-decreasing in t: causal, right-aligned
+ * causal, sliding windows (reference attention.py:242-257, 571-592, 599-667) are all just bounds. */
+int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                        const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch, long long k_pitch,
+                        long long v_pitch, float scale, int causal, cudaStream_t st);
 int sb_attention_bwd_pitch(int T);
 long long sb_attention_bwd_scratch_floats(int T, int heads);
 int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
                      float* scratch, void* dq, void* dk, void* dv, const int* seg_start, const int* seg_end, int T,
                      int heads, int kv_heads, long long q_pitch, long long k_pitch, long long v_pitch, float scale,
                      int causal, cudaStream_t st);
+/* As sb_attention_bwd plus key_qend (int32 [T] or NULL): one past the last query that sees key t (sliding windows: the
+ * dK/dV blocks stop there instead of at the end of the sequence). */
+int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
+                        float* scratch, void* dq, void* dk, void* dv, const int* seg_start, const int* seg_end,
+                        const int* key_qend, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
+                        long long v_pitch, float scale, int causal, cudaStream_t st);
 
 /* Bind `device`'s primary context to the calling thread (tensor-map encoding is a driver call and needs one; PyTorch's
  * autograd worker threads set their device lazily). */

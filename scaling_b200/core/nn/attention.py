@@ -37,6 +37,7 @@ from .tp_ops import (
     all_reduce_scatter_to_sequence_parallel,
     all_shard,
     copy_to_tensor_model_parallel_region,
+    gather_from_sequence_parallel_region,
     get_device,
 )
 
@@ -184,7 +185,15 @@ class ParallelSelfAttention(torch.nn.Module):
     def _sp(self) -> bool:
         return self.topology is not None and self.topology.config.sequence_parallel
 
-    def _project_qkv_rope(self, x: torch.Tensor, position_ids: Optional[torch.Tensor]):
+    def supports_sequence_parallel_shard(self) -> bool:
+        """True when ``forward(..., sequence_parallel_shard=True)`` can take the norm's UNGATHERED [b, s/tp, h] output and
+        run the all-gather inside the q|k|v GEMM (fast projection path, peer communicator present)."""
+        return (self._sp() and not self.qkv_in_one and self.rotary_embedding is not None and not self.key_query_norm
+                and self.kv_replicas == 1 and (self.lora_config is None or self.lora_merged_state)
+                and all(m.get_bias() is None for m in (self.query, self.key, self.value))
+                and get_tp_comm(self.topology, sequence_parallel=True) is not None)
+
+    def _project_qkv_rope(self, x: torch.Tensor, position_ids: Optional[torch.Tensor], sp_shard: bool = False):
         """Fast path for the common layout (separate bias-free q/k/v projections adjacent in the arena, rotary, no
         LoRA / QK-norm): ONE GEMM for q|k|v, then ONE kernel that splits the result and rotates q and k (and one kernel
         back).  Returns None when it does not apply."""
@@ -198,6 +207,16 @@ class ParallelSelfAttention(torch.nn.Module):
         weights = (self.query.weight, self.key.weight, self.value.weight)
         if not OF.qkv_rope_fusable(x, d, rot.dimensions) or OF.fused_view(tuple(w.data for w in weights)) is None:
             return None
+        if sp_shard:
+            sp_comm = get_tp_comm(self.topology, sequence_parallel=True)
+            if not OF.sp_gather_fusable(x, sp_comm, sum(w.shape[0] for w in weights)):
+                return None
+            y = OF.multi_linear_fused(x, weights, sp=sp_comm)  # all-gather(seq) inside the GEMM: y is [b, s, ΣN]
+            if y is None:
+                return None
+            s = y.shape[1]
+            pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
+            return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s, rot.mode, rot.dimensions)
         comm = get_tp_comm(self.topology) if x.is_cuda else None
         if comm is None and not self._sp():
             x = copy_to_tensor_model_parallel_region(x, self.topology)
@@ -268,11 +287,22 @@ class ParallelSelfAttention(torch.nn.Module):
                 position_ids: Optional[torch.Tensor], cumulative_seq_lengths_key: Optional[torch.Tensor] = None,
                 use_cache: bool = False, reset_cache: bool = False, cache_index: int = 0,
                 attention_scores_manipulation: Optional[torch.Tensor] = None,
-                attentions_score_manipulation_log_additive: Union[bool, List[bool]] = True) -> torch.Tensor:
+                attentions_score_manipulation_log_additive: Union[bool, List[bool]] = True,
+                sequence_parallel_shard: bool = False) -> torch.Tensor:
+        """``sequence_parallel_shard``: ``x`` is the norm's ungathered [b, s/tp, h] output (see
+        :meth:`supports_sequence_parallel_shard`); the all-gather then runs inside the projection GEMM."""
+        fused = None
+        if sequence_parallel_shard:
+            fused = self._project_qkv_rope(x, position_ids, sp_shard=True)
+            if fused is None:  # shapes do not fit the fused unit: gather the ordinary way and carry on
+                x = gather_from_sequence_parallel_region(x, self.topology)
         b, s, _ = x.shape
+        if fused is not None:
+            s = s * self.topology.config.model_parallel_size
         T = b * s
         nh, d = self.num_attention_heads_per_partition, self.head_dim
-        fused = self._project_qkv_rope(x, position_ids)
+        if fused is None:
+            fused = self._project_qkv_rope(x, position_ids)
         if fused is not None:
             q, k, v = fused
         else:

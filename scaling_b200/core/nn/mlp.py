@@ -84,7 +84,22 @@ class ParallelSwiGLUMLP(torch.nn.Module):
         self.siglu_weight = ColumnParallelLinear(io_features, f, parallel_output=True, **kw)
         self.dense_out = RowParallelLinear(f, io_features, parallel_input=True, parallel_output=True, **kw)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def supports_sequence_parallel_shard(self) -> bool:
+        """True when ``forward(x, sequence_parallel_shard=True)`` can take the norm's ungathered [b, s/tp, h] output and
+        run the all-gather inside the gate|up dual GEMM."""
+        return (_sp(self.topology) and self.dense_in.get_bias() is None and self.siglu_weight.get_bias() is None
+                and get_tp_comm(self.topology, sequence_parallel=True) is not None)
+
+    def forward(self, x: torch.Tensor, sequence_parallel_shard: bool = False) -> torch.Tensor:
+        if sequence_parallel_shard:
+            sp_comm = get_tp_comm(self.topology, sequence_parallel=True)
+            if OF.sp_gather_fusable(x, sp_comm, self.dense_in.weight.shape[0]) and \
+                    OF.fused_view((self.dense_in.weight.data, self.siglu_weight.weight.data)) is not None:
+                h = OF.swiglu_linear(x, self.dense_in.weight, self.siglu_weight.weight, sp=sp_comm)
+                return _row_parallel_out(self.dense_out, h, self.topology)
+            from .tp_ops import gather_from_sequence_parallel_region
+
+            x = gather_from_sequence_parallel_region(x, self.topology)
         comm = get_tp_comm(self.topology) if x.is_cuda else None
         if comm is None and not _sp(self.topology):
             x = copy_to_tensor_model_parallel_region(x, self.topology)  # one dX all-reduce for gate and up together

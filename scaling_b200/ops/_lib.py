@@ -48,6 +48,7 @@ _SIGS = {
     "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_fwd_peers": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_seq_gather_push": [P, P, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_seq_gather_push_counted": [P, P, P, c_int, c_int, c_int, c_int, c_int, P],
     "sb_seq_scatter_push": [P, P, c_int, c_int, c_int, c_int, c_int, P],
     "sb_sum_slots": [P, P, c_int, c_longlong, P],
     "sb_xent_stats": [P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
@@ -82,7 +83,8 @@ _RET_LL = {
     "sb_gemm2_xent_tiles": [c_int],
 }
 _RET_INT_NOSTREAM = {"sb_grad_sumsq_scratch_floats": [], "sb_bind_device": [c_int],
-                     "sb_gemm2_set_split_workspace": [P, c_ulonglong], "sb_gemm2_set_profile_buffer": [P]}
+                     "sb_gemm2_set_split_workspace": [P, c_ulonglong], "sb_gemm2_set_profile_buffer": [P],
+                     "sb_gemm2_set_gate": [P, c_uint], "sb_seq_gather_chunks_per_tile": []}
 
 
 def lib_path() -> Path:

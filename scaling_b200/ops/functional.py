@@ -322,17 +322,28 @@ class _MultiLinearFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, fused_w, fused_main_grad, comm, *weights):
+    def forward(ctx, x, fused_w, fused_main_grad, comm, sp, *weights):
         shape = x.shape
-        x2 = x.reshape(-1, shape[-1])
-        if not x2.is_contiguous():
-            x2 = x2.contiguous()
-        y = _gemm_nt(x2, fused_w)
-        ctx.save_for_backward(x2, fused_w)
+        ctx.sp = sp
+        if sp is not None:
+            # sequence parallel: x is this rank's [b, s/tp, h] shard.  all-gather -> GEMM as one unit: the
+            # shard is pushed into every rank's gather buffer and the GEMM's TMA producer starts each 256-row tile when
+            # its rows have arrived; only the SHARD is kept for backward.
+            xl = x.contiguous()
+            xg = K.seq_gather_gated(xl, sp)
+            y = K.gemm(xg.view(-1, shape[-1]), fused_w)
+            ctx.save_for_backward(xl, fused_w)
+            shape = xg.shape
+        else:
+            x2 = x.reshape(-1, shape[-1])
+            if not x2.is_contiguous():
+                x2 = x2.contiguous()
+            y = _gemm_nt(x2, fused_w)
+            ctx.save_for_backward(x2, fused_w)
         ctx.comm = comm
         ctx.fused_main_grad = fused_main_grad
         ctx.sizes = [w.shape[0] for w in weights]
-        ctx.x_shape = shape
+        ctx.x_shape = x.shape
         return y.view(*shape[:-1], fused_w.shape[0])
 
     @staticmethod
@@ -342,18 +353,25 @@ class _MultiLinearFn(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         dx = None
-        if ctx.needs_input_grad[0]:
+        if ctx.sp is not None:
+            # dX: dgrad GEMM + reduce-scatter along the sequence in one launch; the wgrad re-gathers the saved shard
+            seq = dy.shape[1]
+            if ctx.needs_input_grad[0]:
+                dx = K.gemm_reduce_scatter(dy2, fused_w, ctx.sp, seq, b_mn=True).view(ctx.x_shape)
+            if any(ctx.needs_input_grad[5:]):
+                x2 = K.seq_all_gather(x2, ctx.sp, clone=False).view(-1, x2.shape[-1])
+        elif ctx.needs_input_grad[0]:
             dx = _gemm_nn_reduce(dy2, fused_w, ctx.comm) if ctx.comm is not None else _gemm_nn(dy2, fused_w)
             dx = dx.view(ctx.x_shape)
         grads: list = [None] * len(ctx.sizes)
-        if not any(ctx.needs_input_grad[4:]):
+        if not any(ctx.needs_input_grad[5:]):
             pass  # frozen weights: no wgrad GEMM at all
         elif ctx.fused_main_grad is not None:
             K.gemm(dy2, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
         else:
             dw = K.gemm(dy2, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
             grads = list(dw.split(ctx.sizes, dim=0))
-        return (dx, None, None, None, *grads)
+        return (dx, None, None, None, None, *grads)
 
 
 def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
@@ -376,15 +394,23 @@ def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
         return None
 
 
-def multi_linear_fused(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None) -> Optional[torch.Tensor]:
-    """x·[W_0; W_1; …]ᵀ as one [..., ΣN_i] tensor when the weights are adjacent in the arena (see multi_linear), else None."""
+def sp_gather_fusable(x_local: torch.Tensor, sp_comm, n_out: int) -> bool:
+    """The all-gather -> GEMM unit applies: peer communicator, [b, s/tp, h] bf16 shard whose sequence slice is whole
+    256-row tiles, an output wide enough for the 2-CTA kernel."""
+    return (sp_comm is not None and x_local.dim() == 3 and native_enabled(x_local) and _PLAIN_GEMM == "native"
+            and K.seq_gather_gated_supported(x_local, sp_comm) and n_out >= 128)
+
+
+def multi_linear_fused(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None, sp=None) -> Optional[torch.Tensor]:
+    """x·[W_0; W_1; …]ᵀ as one [..., ΣN_i] tensor when the weights are adjacent in the arena (see multi_linear), else None.
+    ``sp``: x is a sequence-parallel shard [b, s/tp, h]; it is all-gathered INTO the GEMM (result is [b, s, ΣN_i])."""
     if native_enabled(x) and x.dtype == torch.bfloat16 and all(_aligned(*w.shape) for w in weights) and x.numel() > 0:
         fw = fused_view(tuple(w.data for w in weights))
         if fw is not None:
             mains = [getattr(w, "main_grad", None) for w in weights]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                return _MultiLinearFn.apply(x, fw, fmg, comm, *weights)
+                return _MultiLinearFn.apply(x, fw, fmg, comm, sp, *weights)
     return None
 
 
@@ -397,7 +423,7 @@ def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=
             mains = [getattr(w, "main_grad", None) for w in weights]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                y = _MultiLinearFn.apply(x, fw, fmg, comm, *weights)
+                y = _MultiLinearFn.apply(x, fw, fmg, comm, None, *weights)
                 return tuple(y.split([w.shape[0] for w in weights], dim=-1))
     if comm is not None:
         x = _CopyToRegion.apply(x, comm)
@@ -411,16 +437,24 @@ class _SwiGLUFn(torch.autograd.Function):
     element-wise pass and runs one dgrad + one wgrad GEMM over the concatenated [2F, K] weight."""
 
     @staticmethod
-    def forward(ctx, x, fused_w, fused_main_grad, comm, w_gate, w_up):
+    def forward(ctx, x, fused_w, fused_main_grad, comm, sp, w_gate, w_up):
         ctx.comm = comm
+        ctx.sp = sp
         shape = x.shape
-        x2 = x.reshape(-1, shape[-1])
-        if not x2.is_contiguous():
-            x2 = x2.contiguous()
-        h, pre = K.gemm_swiglu(x2, fused_w, keep_pre=True)
-        ctx.save_for_backward(x2, fused_w, pre)
+        if sp is not None:  # sequence-parallel shard: all-gather -> dual GEMM as one unit (see _MultiLinearFn)
+            xl = x.contiguous()
+            xg = K.seq_gather_gated(xl, sp)
+            h, pre = K.gemm_swiglu(xg.view(-1, shape[-1]), fused_w, keep_pre=True)
+            ctx.save_for_backward(xl, fused_w, pre)
+            shape = xg.shape
+        else:
+            x2 = x.reshape(-1, shape[-1])
+            if not x2.is_contiguous():
+                x2 = x2.contiguous()
+            h, pre = K.gemm_swiglu(x2, fused_w, keep_pre=True)
+            ctx.save_for_backward(x2, fused_w, pre)
         ctx.fused_main_grad = fused_main_grad
-        ctx.x_shape = shape
+        ctx.x_shape = x.shape
         return h.view(*shape[:-1], h.shape[-1])
 
     @staticmethod
@@ -431,21 +465,28 @@ class _SwiGLUFn(torch.autograd.Function):
             dh2 = dh2.contiguous()
         dpre, _ = K.swiglu_bwd(pre, dh2)
         dx = None
-        if ctx.needs_input_grad[0]:
+        if ctx.sp is not None:
+            if ctx.needs_input_grad[0]:
+                dx = K.gemm_reduce_scatter(dpre, fused_w, ctx.sp, dh.shape[1], b_mn=True).view(ctx.x_shape)
+            if any(ctx.needs_input_grad[5:]):
+                x2 = K.seq_all_gather(x2, ctx.sp, clone=False).view(-1, x2.shape[-1])
+        elif ctx.needs_input_grad[0]:
             dx = _gemm_nn_reduce(dpre, fused_w, ctx.comm) if ctx.comm is not None else _gemm_nn(dpre, fused_w)
             dx = dx.view(ctx.x_shape)
         dg = du = None
-        if not any(ctx.needs_input_grad[4:]):
+        if not any(ctx.needs_input_grad[5:]):
             pass
         elif ctx.fused_main_grad is not None:
             K.gemm(dpre, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
         else:
             dw = K.gemm(dpre, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
             dg, du = dw.split(dw.shape[0] // 2, dim=0)
-        return dx, None, None, None, dg, du
+        return dx, None, None, None, None, dg, du
 
 
-def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Parameter, comm=None) -> torch.Tensor:
+def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Parameter, comm=None, sp=None) -> torch.Tensor:
+    """``sp``: x is a sequence-parallel shard [b, s/tp, h] that is all-gathered into the dual GEMM (callers check
+    :func:`sp_gather_fusable` first; the result then covers the full sequence)."""
     if (native_enabled(x) and x.dtype == torch.bfloat16 and _aligned(*w_gate.shape) and w_gate.shape == w_up.shape
             and x.numel() > 0):
         fw = fused_view((w_gate.data, w_up.data))
@@ -453,7 +494,8 @@ def swiglu_linear(x: torch.Tensor, w_gate: torch.nn.Parameter, w_up: torch.nn.Pa
             mains = [getattr(w_gate, "main_grad", None), getattr(w_up, "main_grad", None)]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                return _SwiGLUFn.apply(x, fw, fmg, comm, w_gate, w_up)
+                return _SwiGLUFn.apply(x, fw, fmg, comm, sp, w_gate, w_up)
+    assert sp is None, "sequence-parallel shard given to a path that cannot gather it"
     if comm is not None:
         x = _CopyToRegion.apply(x, comm)
     return F.silu(linear(x, w_gate)) * linear(x, w_up)

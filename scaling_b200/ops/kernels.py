@@ -107,8 +107,11 @@ def gemm(
     if bias is not None:
         assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
     try:
+        entry = _gemm_entry(M, N, a.device)
+        if not a_mn:
+            _apply_gate(a, entry)
         call(
-            _gemm_entry(M, N, a.device), ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
+            entry, ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
             DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
         )
     except RuntimeError as e:
@@ -220,6 +223,7 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True)
     pre = torch.empty((M, 2 * F), dtype=torch.bfloat16, device=x.device) if keep_pre else None
     if _GEMM_IMPL == "2cta" and M >= 256:
         _ensure_split_workspace(x.device)
+        _apply_gate(x, "sb_gemm2_swiglu_bf16")
     call(
         "sb_gemm2_swiglu_bf16" if (_GEMM_IMPL == "2cta" and M >= 256) else "sb_gemm_swiglu_bf16", ptr(x), ptr(w_gate_up), ptr(h), ptr(pre), M, F, K, x.stride(0), w_gate_up.stride(0), F,
         2 * F, 0,
@@ -383,15 +387,50 @@ def seq_peer_ok(x: torch.Tensor, comm) -> bool:
             and x.numel() > 0)
 
 
-def seq_all_gather(x: torch.Tensor, comm) -> torch.Tensor:
+def seq_all_gather(x: torch.Tensor, comm, clone: bool = True) -> torch.Tensor:
     """[b, s/tp, h] -> [b, s, h]: every rank stores its shard into every rank's exchange buffer over NVLink
-    (``sb_seq_gather_push``), one device barrier, and the result is copied out of the (double-buffered) exchange buffer."""
+    (``sb_seq_gather_push``), one device barrier, and the result is copied out of the (double-buffered) exchange buffer.
+    ``clone=False`` hands out the exchange buffer itself: valid until the second next gather, for immediate consumers."""
     b, sl, h = x.shape
     x = x.contiguous()
     buf, ptrs = comm.exchange_buffer("seq_gather", b * sl * comm.size * h * 2)
     call("sb_seq_gather_push", ptr(x), ptrs, comm.size, comm.rank, b, sl, h)
     comm.barrier()
-    return buf.view(torch.bfloat16).view(b, sl * comm.size, h).clone()
+    out = buf.view(torch.bfloat16).view(b, sl * comm.size, h)
+    return out.clone() if clone else out
+
+
+_gates: dict[int, tuple] = {}  # data_ptr of a gated gather buffer -> (counter address, target)
+
+
+def seq_gather_gated_supported(x: torch.Tensor, comm) -> bool:
+    return (_GEMM_IMPL == "2cta" and seq_peer_ok(x, comm) and x.shape[1] % 256 == 0
+            and reduce_scatter_supported(x.shape[0] * x.shape[1] * comm.size, x.shape[1] * comm.size, comm.size))
+
+
+def seq_gather_gated(x: torch.Tensor, comm) -> torch.Tensor:
+    """all-gather -> GEMM, the gather half: every rank stores its [b, s/tp, h] shard into every rank's
+    gather buffer chunk by chunk and bumps a per-row-tile arrival counter (``sb_seq_gather_push_counted``).  NO barrier:
+    the returned [b, s, h] view may ONLY be consumed by :func:`gemm` / :func:`gemm_swiglu` as the A operand — their TMA
+    producer waits per 256-row tile for the counter, so tiles of the local shard start immediately and remote tiles as
+    they land.  The buffer is reused by the second next gated gather of the same shape."""
+    b, sl, h = x.shape
+    tp = comm.size
+    x = x.contiguous()
+    buf, ptrs, gate_local, gate_ptrs, uses = comm.exchange_buffer_gated(f"sp_gate_{b}_{sl}_{h}", b * sl * tp * h * 2)
+    call("sb_seq_gather_push_counted", ptr(x), ptrs, gate_ptrs, tp, comm.rank, b, sl, h)
+    lib = _lib.load(required=True)
+    out = buf.view(torch.bfloat16).view(b, sl * tp, h)
+    _gates[out.data_ptr()] = (gate_local, (uses * int(lib.sb_seq_gather_chunks_per_tile())) & 0xFFFFFFFF)
+    return out
+
+
+def _apply_gate(a: torch.Tensor, entry: str) -> None:
+    g = _gates.get(a.data_ptr())
+    if g is not None:
+        assert entry.startswith("sb_gemm2"), "a gated gather buffer can only feed the 2-CTA GEMM kernels"
+        rc = _lib.load(required=True).sb_gemm2_set_gate(g[0], g[1])
+        assert rc == 0
 
 
 def seq_reduce_scatter(x: torch.Tensor, comm) -> torch.Tensor:

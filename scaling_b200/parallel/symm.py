@@ -106,7 +106,21 @@ class TPComm:
         return self.calls, self._data_ptrs[parity], self._flag_ptrs[parity]
 
     # ---- exchange buffers (embedding rows, sequence-parallel gathers) ---------------------------------------------
-    def exchange_buffer(self, tag: str, nbytes: int):
+    _GATE_BYTES = 64 * 1024  # u32 arrival counters per buffer half (16 Ki row tiles)
+
+    def exchange_buffer_gated(self, tag: str, nbytes: int):
+        """As :meth:`exchange_buffer`, plus per-half arrival counters for the gated all-gather -> GEMM path: returns
+        (local tensor, peer data pointers, local counter address, peer counter pointers, uses of this half so far
+        including this one).  Every use of a tag must have the same shape (counters count uses)."""
+        view, ptrs = self.exchange_buffer(tag, nbytes, _gates=True)
+        ent = self._xbufs[tag]
+        half = ent["calls"] & 1
+        off = 2 * ent["bytes"] + half * self._GATE_BYTES
+        arr = ctypes.c_ulonglong * self.size
+        uses = (ent["calls"] + 1) // 2 if half else ent["calls"] // 2
+        return view, ptrs, ent["ptrs"][self.rank] + off, arr(*[p + off for p in ent["ptrs"]]), uses
+
+    def exchange_buffer(self, tag: str, nbytes: int, _gates: bool = False):
         """(local tensor, peer pointer array) of a double-buffered symmetric byte buffer named ``tag``: peers store into
         it with plain NVLink stores, a :meth:`barrier` publishes them.  Successive calls alternate between two halves,
         so a rank that is one call ahead never overwrites data a slower peer is still reading (it cannot get two calls
@@ -117,8 +131,9 @@ class TPComm:
         if ent is None or ent["bytes"] < nbytes:
             torch.cuda.synchronize(self.device)
             cap = (max(nbytes, 1 << 20) + 65535) // 65536 * 65536
-            buf = symm_mem.empty(2 * cap, dtype=torch.uint8, device=self.device)
+            buf = symm_mem.empty(2 * cap + 2 * self._GATE_BYTES, dtype=torch.uint8, device=self.device)
             hdl = symm_mem.rendezvous(buf, self.group.group_name)
+            buf.zero_()  # arrival counters start at zero
             torch.cuda.synchronize(self.device)
             dist.barrier(group=self.group)
             ent = self._xbufs[tag] = {"bytes": cap, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs],

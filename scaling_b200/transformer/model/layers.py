@@ -369,18 +369,24 @@ class TransformerLayer(TransformerLayerBaseIO):
         use_cache, reset_cache, cache_index, log_add = (False, False, 0, True) if s is None else \
             (s.use_cache, s.reset_cache, s.cache_index, s.control_log_additive_batch)
         h = x.activations
-        a = self.self_attention(self.input_layernorm(h), cumulative_seq_lengths=x.cumulative_seq_lengths,
+        # sequence parallel on GPU: hand the norms' UNGATHERED shards to attention / MLP, whose first GEMM gathers them
+        # over NVLink tile by tile (all-gather -> GEMM as one unit) instead of an all-gather in between
+        shard_attn = h.is_cuda and getattr(self.self_attention, "supports_sequence_parallel_shard", lambda: False)()
+        shard_mlp = h.is_cuda and getattr(self.mlp, "supports_sequence_parallel_shard", lambda: False)()
+        extra = {"sequence_parallel_shard": True} if shard_attn else {}
+        a = self.self_attention(self.input_layernorm(h, gather=not shard_attn),
+                                cumulative_seq_lengths=x.cumulative_seq_lengths,
                                 position_ids=x.position_ids, use_cache=use_cache, reset_cache=reset_cache,
                                 cache_index=cache_index, attention_scores_manipulation=x.attention_scores_manipulation,
-                                attentions_score_manipulation_log_additive=log_add)
+                                attentions_score_manipulation_log_additive=log_add, **extra)
         a = _dropout(a, self.p_attn, self.training, self.topology)
         if hasattr(self, "attn_adapter_name"):
             h = h + a
             h = h + self._adapter(h, self.attn_adapter_name)
-            n = self.post_attention_layernorm(h)
+            n = self.post_attention_layernorm(h, gather=not shard_mlp)
         else:
-            n, h = self.post_attention_layernorm(a, residual=h)  # fused: h <- h + a, n <- norm(h)
-        m = self.mlp(n)
+            n, h = self.post_attention_layernorm(a, residual=h, gather=not shard_mlp)  # fused: h <- h + a, n <- norm(h)
+        m = self.mlp(n, sequence_parallel_shard=True) if shard_mlp else self.mlp(n)
         m = _dropout(m, self.p_mlp, self.training, self.topology)
         h = h + m
         if hasattr(self, "mlp_adapter_name"):

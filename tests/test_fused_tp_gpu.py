@@ -171,6 +171,11 @@ def _train_worker(rank: int, world_size: int, master_port: int, config_dict, fus
     assert _lib.launch_count() > n0
     fused_calls = sum(c.calls for c in symm._COMMS.values())
     assert (fused_calls > 0) == fused, f"fused collective kernels ran {fused_calls} times with fused={fused}"
+    if config_dict["topology"].get("sequence_parallel"):
+        from scaling_b200.ops import kernels as K
+
+        # sequence parallel + peer memory: the all-gathers ran INSIDE the q|k|v and gate|up GEMMs (gated producer)
+        assert bool(K._gates) == fused, f"gated all-gather -> GEMM buffers: {len(K._gates)} with fused={fused}"
     return [m["training/loss"] for m in (metrics or [])]
 
 
