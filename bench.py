@@ -29,6 +29,28 @@ LAYOUTS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}  # n_gpus -> 
 SEQS_PER_GPU = 8  # weak scaling: global batch = 8 * N sequences of 4096 tokens
 
 
+# BASELINE.json configs other than the headline: architecture / training overrides and the layout they are defined on
+PRESETS = {
+    "7b": {},
+    # config 2: examples/transformer_example/config.yml geometry, pure data parallel at every N
+    "example": {"arch": {"vocab_size": 128000, "hidden_size": 256, "num_layers": 4, "num_attention_heads": 2,
+                         "attention_num_kv_heads": None, "attention_qkv_in_one": True, "mlp_factor": 2.5,
+                         "sequence_length": 64, "masked_softmax": {"kernel": "torch", "softmax_in_fp32": True, "scale": 1.0},
+                         "dropout_embedding": 0.1, "dropout_attention_probs": 0.1, "dropout_after_attention": 0.1,
+                         "dropout_after_mlp": 0.1},
+                "seq": 64, "micro_batch": 2, "layout": lambda n: (1, 1, n)},
+    # config 4: Llama-13B geometry with 8 KV heads, TP = 8, activation checkpointing
+    "13b_tp8": {"arch": {"hidden_size": 5120, "num_layers": 40, "num_attention_heads": 40, "attention_num_kv_heads": 8,
+                         "mlp_factor": 2.7}, "layout": lambda n: (n, 1, 1), "act_ckpt": "every_layer"},
+    # config 5: headline geometry + LoRA (rank 64 on q, k, v, dense) + adapters, frozen base, TP4·DP2 on 8 GPUs
+    "7b_lora": {"arch": {"lora_config": {"name": "lora", "rank": 64, "alpha": 64},
+                         "adapter_config": {"name": "adapter", "attention_downsampling_factor": 0.25,
+                                            "mlp_downsampling_factor": 0.25}},
+                "training": {"finetune": True, "finetunable_parameters": ["lora", "adapter"]},
+                "layout": lambda n: (min(n, 4), 1, max(1, n // 4))},
+}
+
+
 def parse_args() -> argparse.Namespace:
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
@@ -41,6 +63,10 @@ def parse_args() -> argparse.Namespace:
     p.add_argument("--act-ckpt", choices=["disabled", "every_layer", "every_pipe_stage"], default="disabled")
     p.add_argument("--seqs-per-gpu", type=int, default=SEQS_PER_GPU)
     p.add_argument("--layout", default=None, help="development: tp,pp,dp override of the headline layout")
+    p.add_argument("--sp", action="store_true", help="development: Megatron sequence parallelism over the TP group")
+    p.add_argument("--preset", default="7b", choices=sorted(PRESETS),
+                   help="7b = the headline (BASELINE config 3); the others are BASELINE configs 2, 4 and 5 "
+                        "(non-headline, recorded in BASELINE.md §4.2)")
     return p.parse_args()
 
 
@@ -57,6 +83,21 @@ def model_config(args: argparse.Namespace, n: int, data_prefix: Path) -> dict:
     """Config dict understood by both TransformerConfig classes (same field names by design)."""
     tp, pp, dp = LAYOUTS[n]
     gb = args.seqs_per_gpu * n
+    cfg = _base_config(args, n, data_prefix, tp, pp, dp, gb)
+    preset = PRESETS[getattr(args, "preset", "7b")]
+    cfg["transformer_architecture"].update(preset.get("arch", {}))
+    cfg["training"].update(preset.get("training", {}))
+    if "act_ckpt" in preset and args.act_ckpt == "disabled":
+        cfg["topology"]["activation_checkpointing_type"] = preset["act_ckpt"]
+    if "micro_batch" in preset:
+        mb = preset["micro_batch"]
+        cfg["topology"]["micro_batch_size"] = mb
+        cfg["topology"]["gradient_accumulation_steps"] = max(1, gb // (dp * mb))
+    cfg["topology"]["sequence_parallel"] = bool(getattr(args, "sp", False))
+    return cfg
+
+
+def _base_config(args, n, data_prefix, tp, pp, dp, gb) -> dict:
     return {
         "logger": {"log_level": "warning", "log_dir": None, "use_wandb": False, "use_tensorboard": False},
         "topology": {
@@ -297,8 +338,13 @@ def result_line(args, n, impl, ms_total, clocks, extra: dict) -> dict:
     }
     line["mfu"] = mfu_block(args, value, n)
     line.update(extra)
-    if args.layers != 32 or args.seqs_per_gpu != SEQS_PER_GPU or args.layout:
-        line["non_headline"] = "development knobs changed the model/batch; not the BASELINE config"
+    if args.layers != 32 or args.seqs_per_gpu != SEQS_PER_GPU or args.layout or args.sp or args.preset != "7b":
+        line["non_headline"] = "development knobs changed the model/batch; not the BASELINE headline config"
+        line["preset"] = args.preset
+        line["sequence_parallel"] = bool(args.sp)
+        if args.preset != "7b":
+            line.pop("mfu", None)  # the MFU block is written for the headline geometry
+            line["config"]["model"] = f"preset {args.preset}"
     return line
 
 
@@ -418,6 +464,12 @@ def run_ours(args: argparse.Namespace) -> None:
 def main() -> None:
     args = parse_args()
     assert args.gpus in LAYOUTS, f"--gpus must be one of {sorted(LAYOUTS)}"
+    preset = PRESETS[args.preset]
+    if "layout" in preset:
+        LAYOUTS[args.gpus] = preset["layout"](args.gpus)
+    if "seq" in preset:
+        global SEQ
+        SEQ = preset["seq"]
     if args.layout:
         tp, pp, dp = (int(v) for v in args.layout.split(","))
         assert tp * pp * dp == args.gpus

@@ -38,10 +38,41 @@ constexpr uint32_t kSmemBytes = kTileBytes * (2 + kKStages + kVStages) + 1024 + 
 constexpr uint32_t kColS = 0;    // Sa at 0, Sb at 128; Px aliases Sx[0, 64)
 constexpr uint32_t kColO = 256;  // Oa at 256, Ob at 384
 
+// Attention-probability dropout (reference core/nn/attention/attention.py:245-258, dropout_p of flash_attn_varlen_func):
+// a stateless per-element hash of (seed, global head, query, key) decides keep / drop, so forward, the dK/dV blocks and
+// the dQ blocks regenerate the SAME mask without storing it, the mask is identical on every replay (activation
+// checkpointing) and differs between the heads of different tensor-parallel ranks (head_offset).
+struct Drop {
+  uint32_t thr;      // drop when hash < thr (thr = p * 2^32); 0 = dropout off
+  uint32_t seed;     // per-call seed (topology dropout seed mixed with the call counter)
+  int head_offset;   // global index of this rank's first head
+  float inv_keep;    // 1 / (1 - p)
+};
+SB_DEVICE bool drop_keep(const Drop& d, int head, int q, int k) {
+  uint32_t x = (uint32_t)q * 0x9E3779B1u + (uint32_t)k * 0x85EBCA77u + (uint32_t)(head + d.head_offset) * 0xC2B2AE3Du + d.seed;
+  x ^= x >> 16;
+  x *= 0x7FEB352Du;
+  x ^= x >> 15;
+  x *= 0x846CA68Bu;
+  x ^= x >> 16;
+  return x >= d.thr;
+}
+
+static inline Drop make_drop(float p, unsigned long long seed, int head_offset) {
+  Drop d;
+  d.thr = p > 0.f ? (uint32_t)((double)p * 4294967296.0) : 0u;
+  if (p > 0.f && d.thr == 0) d.thr = 1;
+  d.seed = (uint32_t)(seed ^ (seed >> 32)) * 0x9E3779B1u + 0x7F4A7C15u;
+  d.head_offset = head_offset;
+  d.inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  return d;
+}
+
 struct Params {
   int T, heads, kv_heads;
   float scale_log2;   // softmax scale * log2(e)
   int causal;
+  Drop drop;
   const int* seg_start;  // [T] first token of the row's sequence
   const int* seg_end;    // [T] one past the last token of the row's sequence
   __nv_bfloat16* out;    // [T, heads, 128]
@@ -92,8 +123,9 @@ SB_DEVICE float fwd_row_max(uint32_t s_tmem, int kv0, int rs, int re) {
   return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
 }
 
-template <bool kMask>
-SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scale_log2, float m_use, float& l0, float& l1) {
+template <bool kMask, bool kDrop>
+SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scale_log2, float m_use, float& l0, float& l1,
+                            const Drop& drop, int head, int row) {
 #pragma unroll 1
   for (int c = 0; c < BKV; c += 32) {
     uint32_t v[32];
@@ -111,6 +143,11 @@ SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scal
       }
       l0 += a;
       l1 += b;
+      if (kDrop) {  // the row sum (softmax normaliser) is taken before dropping; P·V sees the dropped, rescaled values
+        const int key = kv0 + c + 2 * i;
+        a = drop_keep(drop, head, row, key) ? a * drop.inv_keep : 0.f;
+        b = drop_keep(drop, head, row, key + 1) ? b * drop.inv_keep : 0.f;
+      }
       packed[i] = pack_bf16(a, b);
     }
     tmem_st_32x32b_x16(s_tmem + c / 2, packed);
@@ -286,10 +323,16 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
       const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
       // pass 2: p = exp2(s·scale − m_ref), row sum, bf16 pairs written over the already consumed S columns
       float l0 = 0.f, l1 = 0.f;
-      if (need_mask)
-        fwd_exp_pack<true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1);
-      else
-        fwd_exp_pack<false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1);
+      if (p.drop.thr) {
+        if (need_mask)
+          fwd_exp_pack<true, true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+        else
+          fwd_exp_pack<false, true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+      } else if (need_mask) {
+        fwd_exp_pack<true, false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+      } else {
+        fwd_exp_pack<false, false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+      }
       l += l0 + l1;
       tmem_st_wait();
       if (j > 0) {
@@ -396,19 +439,21 @@ int make_map(CUtensorMap* m, const void* ptr, uint64_t width, uint64_t rows, uin
 // right-aligned causal for decoding, sliding windows (seg_start[t] = max(sequence start, t - window)), documents.
 extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                                    const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
-                                   long long k_pitch, long long v_pitch, float scale, int causal, cudaStream_t stream);
+                                   long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
+                                   unsigned long long dropout_seed, int head_offset, cudaStream_t stream);
 extern "C" int sb_attention_fwd(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                                 const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                                 long long v_pitch, float scale, int causal, cudaStream_t stream) {
   return sb_attention_fwd_ex(q, k, v, out, lse, seg_start, seg_end, T, T, heads, kv_heads, q_pitch, k_pitch, v_pitch, scale,
-                             causal, stream);
+                             causal, 0.f, 0ull, 0, stream);
 }
 extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                                    const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
-                                   long long k_pitch, long long v_pitch, float scale, int causal, cudaStream_t stream) {
+                                   long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
+                                   unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
-  if (heads % kv_heads || Tk <= 0 || (causal && Tk != T)) return -1;
+  if (heads % kv_heads || Tk <= 0 || (causal && Tk != T) || dropout_p < 0.f || dropout_p >= 1.f) return -1;
   CUtensorMap mq, mk, mv;
   if (make_map(&mq, q, (uint64_t)heads * D, T, q_pitch)) return -2;
   if (make_map(&mk, k, (uint64_t)kv_heads * D, Tk, k_pitch)) return -2;
@@ -416,6 +461,7 @@ extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, 
   Params p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale_log2 = scale * 1.4426950408889634f, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.out = (__nv_bfloat16*)out, p.lse = lse;
+  p.drop = make_drop(dropout_p, dropout_seed, head_offset);
   static sb::PerDeviceOnce once;
   if (once.first())
     SB_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
@@ -454,6 +500,7 @@ struct BwdParams {
   const int* seg_start;
   const int* seg_end;
   const int* key_qend;  // optional [T]: one past the last query that sees key t (tighter than seg_end under a window)
+  Drop drop;
   const float* lse2;    // [heads, Tp] lse · log2(e)   (Tp = padded pitch, multiple of 64 and > T)
   const float* delta;   // [heads, Tp] Σ_d dO·O
   int Tp;
@@ -520,9 +567,9 @@ SB_DEVICE void store_row_bf16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
 
 // ------------------------------------------------------------------------------------------------- dK / dV
 
-template <bool kMask>
+template <bool kMask, bool kDrop>
 SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_lse2, const float* st_del, int qs0, int key,
-                                   bool key_ok, const BwdParams& p) {
+                                   bool key_ok, const BwdParams& p, int head) {
 #pragma unroll 1
   for (int c = 0; c < BS; c += 32) {
     uint32_t s[32], dp[32];
@@ -547,8 +594,14 @@ SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_l
                            key < (p.causal ? qq + 1 : __ldg(p.seg_end + qc));
           if (!vis) pr = 0.f;
         }
+        float dpe = __uint_as_float(dp[2 * i + e]);
         pv[e] = pr;
-        ds[e] = pr * (__uint_as_float(dp[2 * i + e]) - dl[e]) * p.scale;
+        if (kDrop) {  // dV sees the dropped, rescaled probabilities; dS = P ∘ (D ∘ dP / (1 − p) − delta)
+          const bool keep = drop_keep(p.drop, head, qs0 + c + 2 * i + e, key);
+          pv[e] = keep ? pr * p.drop.inv_keep : 0.f;
+          dpe = keep ? dpe * p.drop.inv_keep : 0.f;
+        }
+        ds[e] = pr * (dpe - dl[e]) * p.scale;
       }
       pp[i] = pack_bf16(pv[0], pv[1]);
       pp[i + 1] = pack_bf16(pv[2], pv[3]);
@@ -691,10 +744,17 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
       const float* st_lse2 = stats + (it % kRing) * 2 * BS;  // staged by the producer together with Q_sub / dO_sub
       const float* st_del = st_lse2 + BS;
       const uint32_t t_s = tmem + lane_base + (it & 1) * 128, t_p = t_s + 64;
-      if (sub_mask[it % n_sub])
-        dkdv_softmax_chunks<true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p);
-      else
-        dkdv_softmax_chunks<false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p);
+      const int hq = kvh * group + it / n_sub;  // query head of this sub-tile (for the dropout mask)
+      if (p.drop.thr) {
+        if (sub_mask[it % n_sub])
+          dkdv_softmax_chunks<true, true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+        else
+          dkdv_softmax_chunks<false, true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+      } else if (sub_mask[it % n_sub]) {
+        dkdv_softmax_chunks<true, false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+      } else {
+        dkdv_softmax_chunks<false, false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+      }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -720,9 +780,9 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
 
 // ------------------------------------------------------------------------------------------------- dQ
 
-template <bool kMask>
+template <bool kMask, bool kDrop>
 SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, int re, float scale_log2, float lse2,
-                                 float del, float scale) {
+                                 float del, float scale, const Drop& drop, int head, int row) {
 #pragma unroll 1
   for (int c = 0; c < BS; c += 32) {
     uint32_t s[32], dp[32];
@@ -740,7 +800,9 @@ SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, in
           const int kk = ks0 + c + 2 * i + e;
           if (!(kk >= rs && kk < re)) pr = 0.f;
         }
-        d2[e] = pr * (__uint_as_float(dp[2 * i + e]) - del) * scale;
+        float dpe = __uint_as_float(dp[2 * i + e]);
+        if (kDrop) dpe = drop_keep(drop, head, row, ks0 + c + 2 * i + e) ? dpe * drop.inv_keep : 0.f;
+        d2[e] = pr * (dpe - del) * scale;
       }
       pd[i] = pack_bf16(d2[0], d2[1]);
     }
@@ -864,10 +926,16 @@ SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, 
       tc_fence_after();
       const bool need_mask = __any_sync(0xffffffffu, (ks0 < rs) || (ks0 + BS > re));
       const uint32_t t_s = tmem + lane_base + (it & 1) * 128, t_p = t_s + 64;
-      if (need_mask)
-        dq_softmax_chunks<true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale);
-      else
-        dq_softmax_chunks<false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale);
+      if (p.drop.thr) {
+        if (need_mask)
+          dq_softmax_chunks<true, true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+        else
+          dq_softmax_chunks<false, true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+      } else if (need_mask) {
+        dq_softmax_chunks<true, false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+      } else {
+        dq_softmax_chunks<false, false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+      }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -948,19 +1016,19 @@ extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* 
                                    const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
                                    const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
                                    long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
-                                   cudaStream_t stream);
+                                   float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream);
 extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
                                 const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
                                 const int* seg_end, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                                 long long v_pitch, float scale, int causal, cudaStream_t stream) {
   return sb_attention_bwd_ex(dout, q, k, v, out, lse, scratch, dq, dk, dv, seg_start, seg_end, nullptr, T, heads, kv_heads,
-                             q_pitch, k_pitch, v_pitch, scale, causal, stream);
+                             q_pitch, k_pitch, v_pitch, scale, causal, 0.f, 0ull, 0, stream);
 }
 extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out,
                                    const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
                                    const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
                                    long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
-                                   cudaStream_t stream) {
+                                   float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
   if (heads % kv_heads) return -1;
@@ -973,6 +1041,7 @@ extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* 
   BwdParams p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale = scale, p.scale_log2 = scale * kLog2e, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.key_qend = key_qend, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
+  p.drop = make_drop(dropout_p, dropout_seed, head_offset);
   p.dq = (__nv_bfloat16*)dq, p.dk = (__nv_bfloat16*)dk, p.dv = (__nv_bfloat16*)dv;
   static sb::PerDeviceOnce once;
   static bool separate = false;  // SCALING_B200_ATTN_BWD_SEPARATE=1: two launches (dK/dV, then dQ), for A/B timing

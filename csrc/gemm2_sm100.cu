@@ -68,8 +68,16 @@ struct Params {
   // split-K tail: the last, partial wave of tiles is cut along K into `split` parts so that it fills the machine
   int full_tiles;   // tiles [0, full_tiles) run whole; the remaining `num_tiles - full_tiles` are split
   int split;        // parts per tail tile (1 = no splitting)
-  float* split_ws;  // [tail tile][part][cta half] partial accumulators, 128x256 fp32 each
-  unsigned int* split_counters;  // [tail tile][cta half] arrivals; the last arriver reduces and resets
+  float* split_ws;  // parked partial accumulators, 128x256 fp32 per (slot, cta half); slot: see part_slot()
+  unsigned int* split_counters;  // [counter index][cta half] arrivals; the last arriver reduces and resets
+  // stream-K tail (stream_k = 1): tiles [0, sk_first_tile) run whole, round-robin over the clusters in waves (neighbouring
+  // tiles in flight together: the A / B panels stay in L2); the flattened (tile-major) k-block space of the remaining
+  // one-to-two waves of tiles is cut into one contiguous range per cluster, so every cluster does the same amount of MMA
+  // work and there is no partial last wave.  Tiles that straddle a range boundary are computed in parts that meet in
+  // split_ws exactly like the split tail.  (Cutting ALL tiles that way was measured 1.5x slower: 74 clusters streaming 74
+  // distant regions of the tile space lose the L2 reuse of the operand panels.)
+  int stream_k;
+  int sk_first_tile;
   // kAllReduce only
   int tp_rank, tp_size;
   uint32_t epoch;
@@ -241,36 +249,99 @@ SB_DEVICE int tile_owner(const Params& p, int t, int tm) {
   return -1;
 }
 
-// Work unit u of the persistent schedule -> (tile, k-block range, part index or -1 when the tile is not split).
+// Work unit of the persistent schedule: (tile, k-block range, part index or -1 when the tile is not split, parts of
+// the tile).
 struct Unit {
-  int tile, kb0, kb1, part;
+  int tile, kb0, kb1, part, nparts;
 };
 SB_DEVICE Unit get_unit(int u, const Params& p, int k_blocks) {
   Unit w;
   if (u < p.full_tiles) {
-    w.tile = u, w.kb0 = 0, w.kb1 = k_blocks, w.part = -1;
+    w.tile = u, w.kb0 = 0, w.kb1 = k_blocks, w.part = -1, w.nparts = 1;
   } else {
     const int r = u - p.full_tiles;
     w.tile = p.full_tiles + r / p.split;
     w.part = r % p.split;
+    w.nparts = p.split;
     w.kb0 = (int)((long long)w.part * k_blocks / p.split);
     w.kb1 = (int)((long long)(w.part + 1) * k_blocks / p.split);
   }
   return w;
 }
+// stream-K bookkeeping over the flattened k-block index x in [0, total): cluster c owns [sk_lo(c), sk_lo(c + 1))
+SB_DEVICE long long sk_lo(int c, long long total, int nc) { return (long long)c * total / nc; }
+SB_DEVICE int sk_cluster_of(long long x, long long total, int nc) { return (int)(((x + 1) * nc + total - 1) / total) - 1; }
+// The units of one cluster, for all three roles (producer, MMA issuer, epilogue) to iterate identically.
+struct Sched {
+  int stream_k, cluster_id, nc, k_blocks, n;
+  int n_dp;      // stream-K: whole tiles of this cluster before its stream-K range
+  int f_tiles;   // stream-K: first tile of the stream-K region
+  long long total, lo, hi;  // flattened k-block space of the stream-K region and this cluster's range in it
+  int t_first;   // first tile (relative to f_tiles) of this cluster's range
+};
+SB_DEVICE Sched make_sched(const Params& p, int cluster_id, int nc, int k_blocks, int num_units) {
+  Sched s;
+  s.stream_k = p.stream_k, s.cluster_id = cluster_id, s.nc = nc, s.k_blocks = k_blocks;
+  s.n_dp = 0, s.f_tiles = 0;
+  if (p.stream_k) {
+    s.f_tiles = p.sk_first_tile;
+    s.n_dp = s.f_tiles / nc;  // sk_first_tile is a multiple of the cluster count
+    s.total = (long long)(p.tiles_m * p.tiles_n - s.f_tiles) * k_blocks;
+    s.lo = sk_lo(cluster_id, s.total, nc), s.hi = sk_lo(cluster_id + 1, s.total, nc);
+    s.t_first = (int)(s.lo / k_blocks);
+    s.n = s.n_dp + (s.hi > s.lo ? (int)((s.hi - 1) / k_blocks) - s.t_first + 1 : 0);
+  } else {
+    s.total = 0, s.lo = s.hi = 0, s.t_first = 0;
+    s.n = cluster_id < num_units ? (num_units - cluster_id + nc - 1) / nc : 0;
+  }
+  return s;
+}
+SB_DEVICE Unit sched_unit(const Sched& s, const Params& p, int i) {
+  if (!s.stream_k) return get_unit(s.cluster_id + i * s.nc, p, s.k_blocks);
+  Unit w;
+  if (i < s.n_dp) {
+    w.tile = s.cluster_id + i * s.nc, w.kb0 = 0, w.kb1 = s.k_blocks, w.part = -1, w.nparts = 1;
+    return w;
+  }
+  const int rel = s.t_first + (i - s.n_dp);  // tile index inside the stream-K region
+  w.tile = s.f_tiles + rel;
+  const long long t0 = (long long)rel * s.k_blocks, t1 = t0 + s.k_blocks;
+  const long long g0 = s.lo > t0 ? s.lo : t0, g1 = s.hi < t1 ? s.hi : t1;
+  w.kb0 = (int)(g0 - t0), w.kb1 = (int)(g1 - t0);
+  if (w.kb0 == 0 && w.kb1 == s.k_blocks) {
+    w.part = -1, w.nparts = 1;
+  } else {
+    const int c_first = sk_cluster_of(t0, s.total, s.nc), c_last = sk_cluster_of(t1 - 1, s.total, s.nc);
+    w.part = s.cluster_id - c_first, w.nparts = c_last - c_first + 1;
+  }
+  return w;
+}
+// Where part q of a split tile parks its accumulator, and which arrival counter the tile uses.
+SB_DEVICE int part_slot(const Sched& s, const Params& p, int tile, int q) {
+  if (!s.stream_k) return (tile - p.full_tiles) * p.split + q;
+  // stream-K: a cluster parks at most two partials per launch — the unit that begins its range (slot 0) and the one
+  // that ends it (slot 1)
+  const long long t0 = (long long)(tile - s.f_tiles) * s.k_blocks;
+  const int c = sk_cluster_of(t0, s.total, s.nc) + q;
+  const long long lo = sk_lo(c, s.total, s.nc);
+  return c * 2 + ((lo > t0 ? lo : t0) == lo ? 0 : 1);
+}
+SB_DEVICE int part_counter(const Sched& s, const Params& p, int tile) { return s.stream_k ? tile : tile - p.full_tiles; }
 constexpr int kCtaAccFloats = 128 * 256;
 // Partial accumulators are stored "float4-column-major": [group of 4 columns][row][4] so that a warp (lane = row) writes
 // and later reads 512 contiguous bytes per instruction.
-SB_DEVICE float4* split_slot(const Params& p, int tail_tile, int part, uint32_t half) {
-  return reinterpret_cast<float4*>(p.split_ws + ((size_t)(tail_tile * p.split + part) * 2 + half) * kCtaAccFloats);
+SB_DEVICE float4* split_slot(const Params& p, int slot, uint32_t half) {
+  return reinterpret_cast<float4*>(p.split_ws + ((size_t)slot * 2 + half) * kCtaAccFloats);
 }
 // v[0..n) += the other parts' partials of columns [c, c+n) of this thread's row, in part order (own registers take the
 // place of part `own`), so the sum is the same whichever part arrives last.
 template <int kN>
-SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, int tail_tile, int own, uint32_t half, int row_in_cta, int c) {
+SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, const Sched& sc, const Unit& w, uint32_t half, int row_in_cta,
+                                   int c) {
   float acc[kN];
   bool first = true;
-  for (int q = 0; q < p.split; ++q) {
+  const int own = w.part;
+  for (int q = 0; q < w.nparts; ++q) {
     if (q == own) {
       if (first) {
 #pragma unroll
@@ -280,7 +351,7 @@ SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, int tail_tile, i
         for (int i = 0; i < kN; ++i) acc[i] += __uint_as_float(v[i]);
       }
     } else {
-      const float4* src = split_slot(p, tail_tile, q, half) + (size_t)(c >> 2) * 128 + row_in_cta;
+      const float4* src = split_slot(p, part_slot(sc, p, w.tile, q), half) + (size_t)(c >> 2) * 128 + row_in_cta;
 #pragma unroll
       for (int g = 0; g < kN / 4; ++g) {
         const float4 x = __ldcg(src + (size_t)g * 128);
@@ -316,6 +387,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const int kb_main = (p.K + BK - 1) / BK;
   const int k_blocks = kb_main + p.kb_extra;
   const int num_units = p.full_tiles + (num_tiles - p.full_tiles) * p.split;
+  const Sched sched = make_sched(p, blockIdx.x >> 1, gridDim.x >> 1, k_blocks, num_units);
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
 
@@ -351,8 +423,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int u = cluster_id; u < num_units; u += num_clusters) {
-        const Unit w = get_unit(u, p, k_blocks);
+      for (int ui = 0; ui < sched.n; ++ui) {
+        const Unit w = sched_unit(sched, p, ui);
         int tm, tn;
         tile_coords(w.tile, p.tiles_m, p.tiles_n, tm, tn);
         if (p.gate) {
@@ -406,8 +478,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int u = cluster_id; u < num_units; u += num_clusters) {
-        const Unit w = get_unit(u, p, k_blocks);
+      for (int ui = 0; ui < sched.n; ++ui) {
+        const Unit w = sched_unit(sched, p, ui);
         mbar_wait(&bars->acc_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -626,8 +698,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     const int ew = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int u = cluster_id; u < num_units; u += num_clusters) {
-      const Unit w = get_unit(u, p, k_blocks);
+    for (int ui = 0; ui < sched.n; ++ui) {
+      const Unit w = sched_unit(sched, p, ui);
       int tm, tn;
       tile_coords(w.tile, p.tiles_m, p.tiles_n, tm, tn);
       const int row_in_cta = ew * 32 + lane;
@@ -637,10 +709,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
       const bool row_ok = row < p.M;
       const bool split = w.part >= 0;
-      const int tail_tile = w.tile - p.full_tiles;
       if (split) {
         // park this part's accumulator, then find out whether the other parts are already in
-        float4* mine = split_slot(p, tail_tile, w.part, rank) + row_in_cta;
+        float4* mine = split_slot(p, part_slot(sched, p, w.tile, w.part), rank) + row_in_cta;
 #pragma unroll 1
         for (int c = 0; c < BN; c += 32) {
           uint32_t v[32];
@@ -655,9 +726,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         __threadfence();
         asm volatile("bar.sync 1, 128;\n" ::: "memory");
         if (ew == 0 && lane == 0) {
-          unsigned int* ctr = p.split_counters + tail_tile * 2 + rank;
+          unsigned int* ctr = p.split_counters + part_counter(sched, p, w.tile) * 2 + rank;
           const unsigned int old = atomicAdd(ctr, 1u);
-          const bool last = old == (unsigned int)(p.split - 1);
+          const bool last = old == (unsigned int)(w.nparts - 1);
           if (last) *ctr = 0;  // every part has arrived: leave the counter clean for the next launch
           bars->split_last = last ? 1u : 0u;
         }
@@ -734,8 +805,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           tmem_ld_32x32b_x16(taddr + BN / 2 + c, u);
           tmem_ld_wait();
           if (split) {
-            split_reduce_chunk<16>(g, p, tail_tile, w.part, rank, row_in_cta, c);
-            split_reduce_chunk<16>(u, p, tail_tile, w.part, rank, row_in_cta, BN / 2 + c);
+            split_reduce_chunk<16>(g, p, sched, w, rank, row_in_cta, c);
+            split_reduce_chunk<16>(u, p, sched, w, rank, row_in_cta, BN / 2 + c);
           }
           if (row_ok && n0 + c < p.N) {
             uint32_t o[8], pg[8], pu[8];
@@ -780,7 +851,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           uint32_t v[32];
           tmem_ld_32x32b_x32(taddr + c, v);
           tmem_ld_wait();
-          if (split) split_reduce_chunk<32>(v, p, tail_tile, w.part, rank, row_in_cta, c);
+          if (split) split_reduce_chunk<32>(v, p, sched, w, rank, row_in_cta, c);
           const int col = n0 + c;
           if (!row_ok || col >= p.N) continue;
           if (col + 32 <= p.N) {
@@ -893,8 +964,19 @@ struct SplitWorkspace {
   unsigned int* counters = nullptr;
 };
 static SplitWorkspace g_split_ws[64];
-static size_t split_partial_bytes() { return (size_t)num_sms() * kCtaAccFloats * sizeof(float); }
-static size_t split_counter_bytes() { return (size_t)num_sms() * sizeof(unsigned int); }
+// partials: two slots per cluster and CTA half (stream-K) >= the split tail's one slot per tail part; counters: one per
+// tile and CTA half
+constexpr int kMaxStreamKTiles = 32768;
+static size_t split_partial_bytes() { return (size_t)2 * num_sms() * kCtaAccFloats * sizeof(float); }
+static size_t split_counter_bytes() { return (size_t)2 * kMaxStreamKTiles * sizeof(unsigned int); }
+static bool stream_k_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("SCALING_B200_GEMM_STREAMK");
+    on = (e && e[0] == '1') ? 1 : 0;  // opt-in until the measured A/B says otherwise
+  }
+  return on == 1;
+}
 static SplitWorkspace* split_workspace() {
   int dev = 0;
   cudaGetDevice(&dev);
@@ -991,8 +1073,26 @@ static int launch(const Maps& m, Params& p, cudaStream_t stream, int max_ctas) {
       }
     }
   }
-  const int units = p.full_tiles + (tiles - p.full_tiles) * p.split;
-  const int clusters = units < width ? units : width;
+  int units = p.full_tiles + (tiles - p.full_tiles) * p.split;
+  int clusters = units < width ? units : width;
+  // stream-K tail (SCALING_B200_GEMM_STREAMK=1): whenever the tiles do not fill whole waves, the last full
+  // wave and the partial one are balanced by k-blocks instead of whole tiles (see Params::stream_k).  256 tiles on 74
+  // clusters then take 3.46 tile-times instead of 4, and a 16-tile GEMM with a long K occupies all 74 clusters instead of
+  // 16.  Supersedes the split tail above.
+  p.stream_k = 0;
+  if (EPI != kAllReduce && EPI != kXentStats && split_enabled() && stream_k_enabled() && tiles % width != 0 &&
+      tiles <= kMaxStreamKTiles) {
+    // whole waves except the last full one run as plain tiles; the last full wave + the partial one are balanced
+    const int first = tiles > width ? (tiles / width - 1) * width : 0;
+    const long long total = (long long)(tiles - first) * ((p.K + BK - 1) / BK + p.kb_extra);
+    if (total / width >= 8) {
+      if (SplitWorkspace* w = split_workspace()) {
+        p.stream_k = 1, p.sk_first_tile = first, p.full_tiles = tiles, p.split = 1;
+        p.split_ws = w->ws, p.split_counters = w->counters;
+        clusters = width;
+      }
+    }
+  }
   if (EPI == kAllReduce)
     kern<<<clusters * 2, kArThreads, kArSmemBytes, stream>>>(m.a, m.b, m.a2, m.b2, p);
   else

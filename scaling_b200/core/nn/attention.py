@@ -346,6 +346,11 @@ class ParallelSelfAttention(torch.nn.Module):
                       scale=self.scaling_factor, cu_seqlens_k=cu_k, max_seqlen_k=max_k,
                       dropout_p=self.dropout_attention_probs, training=self.training,
                       deterministic=self.masked_softmax_config.deterministic_flash_attn_bwd)
+        if self.dropout_attention_probs > 0.0 and self.training and self.topology is not None and not dense_path:
+            # counter-based mask: same on every replay of this call (activation checkpointing), distinct per global head
+            t = self.topology
+            common["dropout_seed"] = (t.dropout_seed ^ (t.next_dropout_offset() * 0x9E3779B97F4A7C15)) & (2**63 - 1)
+            common["head_offset"] = t.model_parallel_rank * nh
         if dense_path:
             manip = attention_scores_manipulation
             if manip is not None and manip.dim() == 4:  # [b, heads|1, s, s] -> [heads|1, T, T] block diagonal

@@ -133,14 +133,18 @@ class ParallelModule(PipePartitionedModule, Generic[BaseLossInputGeneric, BaseDa
         dev = topo.device
         cont = use_continuous_recommunication
         # forward traffic comes from the previous stage, gradients from the next
-        self.communicator_in = PipeCommunicator(dev, recv_grads=False, recv_data=True, use_continuous_recommunication=cont)
-        self.communicator_out = PipeCommunicator(dev, recv_grads=True, recv_data=False, use_continuous_recommunication=cont)
+        fwd_group, bwd_group = topo.pipe_p2p_groups
+        groups = dict(group=fwd_group, grad_group=bwd_group)
+        self.communicator_in = PipeCommunicator(dev, recv_grads=False, recv_data=True, use_continuous_recommunication=cont, **groups)
+        self.communicator_out = PipeCommunicator(dev, recv_grads=True, recv_data=False, use_continuous_recommunication=cont, **groups)
         self.communicator_loss_in = self.communicator_loss_out = None
         if pp > 1:
+            # loss + metrics keep one structure per mode (train / eval): the handshake is cached like the activations'
+            # (the reference re-pickles it every step, communicator.py:256-281)
             if topo.is_first_pipe_parallel_rank:
-                self.communicator_loss_in = PipeCommunicator(dev, False, True, use_continuous_recommunication=True)
+                self.communicator_loss_in = PipeCommunicator(dev, False, True, use_continuous_recommunication=cont, group=bwd_group)
             if topo.is_last_pipe_parallel_rank:
-                self.communicator_loss_out = PipeCommunicator(dev, False, False, use_continuous_recommunication=True)
+                self.communicator_loss_out = PipeCommunicator(dev, False, False, use_continuous_recommunication=cont, group=bwd_group)
         self.profiler = Profiler(profiler_config or ProfilerConfig(), topo)
         self.step_timer = SynchronizedTimer()
         self._mark_tied_main_stage()

@@ -41,12 +41,13 @@ def _wire(t: torch.Tensor, byte_wire: bool) -> torch.Tensor:
 
 class PipeCommunicator:
     def __init__(self, local_device: torch.device, recv_grads: bool, recv_data: bool,
-                 use_continuous_recommunication: bool = False, group: Any = None):
+                 use_continuous_recommunication: bool = False, group: Any = None, grad_group: Any = None):
         self.local_device = local_device
         self.recv_grads_enabled = recv_grads
         self.recv_data_enabled = recv_data
         self.use_continuous_recommunication = use_continuous_recommunication
-        self.group = group
+        self.group = group  # activations (and handshakes)
+        self.grad_group = grad_group if grad_group is not None else group  # gradients travel the other way
         self.byte_wire = local_device.type != "cuda"  # gloo: ship raw bytes, every dtype works
         # cached handshakes, one per mode: training and evaluation messages differ in their requires_grad flags (and
         # possibly shapes), and every rank switches mode at the same step, so each mode negotiates once
@@ -82,21 +83,22 @@ class PipeCommunicator:
             work.wait()
         self._pending.clear()
 
-    def _isend(self, t: torch.Tensor, dst: int) -> None:
+    def _isend(self, t: torch.Tensor, dst: int, grad: bool = False) -> None:
         w = _wire(t, self.byte_wire)
-        self._pending.append((dist.isend(w, dst=dst, group=self.group), w))
+        self._pending.append((dist.isend(w, dst=dst, group=self.grad_group if grad else self.group), w))
 
-    def _recv_into(self, shape: Tuple[int, ...], dtype: torch.dtype, src: int) -> torch.Tensor:
+    def _recv_into(self, shape: Tuple[int, ...], dtype: torch.dtype, src: int, grad: bool = False) -> torch.Tensor:
+        group = self.grad_group if grad else self.group
         wire_dtype = torch.uint8 if dtype == torch.bool else dtype
         if self.byte_wire:
             itemsize = torch.empty((), dtype=wire_dtype).element_size()
             n = int(torch.Size(shape).numel())
             buf = torch.empty(n * itemsize, dtype=torch.uint8, device=self.local_device)
-            dist.recv(buf, src=src, group=self.group)
+            dist.recv(buf, src=src, group=group)
             out = buf.view(wire_dtype).reshape(shape)
         else:
             out = torch.empty(shape, dtype=wire_dtype, device=self.local_device)
-            dist.irecv(out, src=src, group=self.group).wait()
+            dist.irecv(out, src=src, group=group).wait()
         return out.to(torch.bool) if dtype == torch.bool else out
 
     def _send_object(self, obj: Any, dst: int) -> None:
@@ -146,7 +148,7 @@ class PipeCommunicator:
         for x in leaves:
             if torch.is_tensor(x) and x.requires_grad:
                 g = x.grad if x.grad is not None else torch.zeros_like(x)
-                self._isend(g, target_global_rank)
+                self._isend(g, target_global_rank, grad=True)
 
     def recv_gradients(self, data: Any, origin_global_rank: int) -> GradOutput:
         """``data`` is the pytree that was sent as stage output; returns the tensors to backpropagate with their
@@ -156,7 +158,7 @@ class PipeCommunicator:
         for x in leaves:
             if torch.is_tensor(x) and x.requires_grad:
                 tensors.append(x)
-                grads.append(self._recv_into(tuple(x.shape), x.dtype, origin_global_rank))
+                grads.append(self._recv_into(tuple(x.shape), x.dtype, origin_global_rank, grad=True))
         return GradOutput(tensors, grads)
 
 

@@ -207,7 +207,19 @@ class Topology:
             g = dist.new_group(ranks)
             if self.config.global_rank in ranks:
                 self._mp_group = g
+        # pipeline p2p gets communicators of its own — activations one way, gradients the other — so that a send waiting
+        # for its receiver serialises neither with the collectives on the world group nor with traffic in the other
+        # direction (the reference sends everything through the world group, communicator.py:381-500)
+        self._p2p_groups = (None, None)
+        if self.config.pipe_parallel_size > 1 and os.environ.get("SCALING_B200_P2P_GROUPS", "0") == "1":
+            everyone = list(range(self.config.world_size))
+            self._p2p_groups = (dist.new_group(everyone), dist.new_group(everyone))
         self.is_distributed_initialized = True
+
+    @property
+    def pipe_p2p_groups(self) -> tuple:
+        """(forward-traffic group, backward-traffic group) spanning all ranks, or (None, None) without pipelining."""
+        return getattr(self, "_p2p_groups", (None, None))
 
     def _seed_rng(self, seed: int) -> None:
         base = seed + int(self._grid[self._pp_rank, self._dp_rank, 0])

@@ -58,9 +58,9 @@ _SIGS = {
     "sb_xent_grad": [P, P, P, P, P, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_attention_fwd": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float, c_int, P],
     "sb_attention_fwd_ex": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float,
-                            c_int, P],
+                            c_int, c_float, c_ulonglong, c_int, P],
     "sb_attention_bwd_ex": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
-                            c_float, c_int, P],
+                            c_float, c_int, c_float, c_ulonglong, c_int, P],
     "sb_attention_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
                          c_float, c_int, P],
     "sb_grad_sumsq": [P, c_longlong, c_int, P, P, c_int, P, P],

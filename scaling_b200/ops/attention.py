@@ -108,7 +108,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: t
               causal: bool = True, scale: Optional[float] = None, cu_seqlens_k: Optional[torch.Tensor] = None,
               max_seqlen_k: Optional[int] = None, window: Optional[int] = None, dropout_p: float = 0.0,
               training: bool = False, deterministic: bool = False, softmax_fn=None, dropout_fn=None,
-              scores_manipulation=None, manipulation_log_additive=True) -> torch.Tensor:
+              scores_manipulation=None, manipulation_log_additive=True, dropout_seed: Optional[int] = None,
+              head_offset: int = 0) -> torch.Tensor:
+    """``dropout_seed`` / ``head_offset``: seed of the (stateless) dropout mask of the sm_100a kernel and the global index
+    of the first local head — pass the topology's counter-based seed so that every replay (activation checkpointing)
+    reproduces the mask; without a seed one is drawn from torch's CPU generator."""
     scale = 1.0 / math.sqrt(q.shape[-1]) if scale is None else scale
     cu_k = cu_seqlens_q if cu_seqlens_k is None else cu_seqlens_k
     max_k = max_seqlen_q if max_seqlen_k is None else max_seqlen_k
@@ -121,15 +125,20 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: t
         if fusable:
             from .attention_sm100 import sm100_attention_supported
 
-            # no library kernel behind "auto": what the sm_100a kernel does not cover (attention-probability dropout,
-            # fp16, head dims above 128, gradients through a KV cache) runs the plain PyTorch expression; the flash-attn
+            # no library kernel behind "auto": what the sm_100a kernel does not cover (fp16, head dims above 128,
+            # gradients through a KV cache) runs the plain PyTorch expression; the flash-attn
             # wheel is only used when asked for by name (SCALING_B200_ATTENTION=flash, A/B measurements)
             if sm100_attention_supported(q, k, v, cu_seqlens_q, cu_k, causal, window, p):
                 impl = "sm100"
     if impl == "sm100" and fusable:
         from .attention_sm100 import sm100_attention
 
-        return sm100_attention(q, k, v, cu_seqlens_q, max_seqlen_q, causal, scale, window=window, cu_seqlens_k=cu_k)
+        drop = (0.0, 0, 0)
+        if p > 0.0:
+            seed = int(torch.randint(0, 2**62, (1,)).item()) if dropout_seed is None else int(dropout_seed)
+            drop = (p, seed, head_offset)
+        return sm100_attention(q, k, v, cu_seqlens_q, max_seqlen_q, causal, scale, window=window, cu_seqlens_k=cu_k,
+                               dropout=drop)
     if impl == "flash" and fusable and _flash():
         w = (-1, -1) if not window else (window, 0 if causal else window)
         return _flash()(q.contiguous(), k.contiguous(), v.contiguous(), cu_seqlens_q=cu_seqlens_q.to(torch.int32),

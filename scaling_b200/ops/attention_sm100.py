@@ -14,13 +14,13 @@ _BWD_IMPL = os.environ.get("SCALING_B200_ATTENTION_BWD", "auto")  # auto | sm100
 
 def sm100_attention_supported(q, k, v, cu_q, cu_k, causal, window, dropout_p) -> bool:
     """bf16, head dim <= 128 (smaller heads are zero-padded to the kernel's 128), GQA/MQA, packed sequences, causal or
-    bidirectional, sliding windows; keys may differ from queries (KV-cache decoding) when no gradient is needed.
-    Attention-probability dropout is not implemented in the kernel."""
+    bidirectional, sliding windows, attention-probability dropout (stateless hash mask); keys may differ from queries
+    (KV-cache decoding) when no gradient is needed."""
     lib = _lib.load() if torch.cuda.is_available() else None
     if lib is None or not hasattr(lib, "sb_attention_fwd_ex"):
         return False
     d = q.shape[-1]
-    if not (q.dtype == torch.bfloat16 and d <= 128 and d % 8 == 0 and dropout_p == 0.0 and q.shape[1] % k.shape[1] == 0):
+    if not (q.dtype == torch.bfloat16 and d <= 128 and d % 8 == 0 and 0.0 <= dropout_p < 1.0 and q.shape[1] % k.shape[1] == 0):
         return False
     if cu_q is not cu_k and (q.requires_grad or k.requires_grad or v.requires_grad) and torch.is_grad_enabled():
         return False  # decoding against a cache is forward only
@@ -80,12 +80,14 @@ def window_bounds(cu_seqlens: torch.Tensor, total: int, causal: bool, window: in
     return lo.contiguous(), hi.contiguous(), qend.contiguous()
 
 
-def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float):
+def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float, dropout=(0.0, 0, 0)):
+    """``dropout`` = (p, seed, global index of the first local head)."""
     T, heads, d = q.shape
     out = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     lse = torch.empty((heads, T), dtype=torch.float32, device=q.device)
     call("sb_attention_fwd_ex", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, k.shape[0],
-         heads, k.shape[1], q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal))
+         heads, k.shape[1], q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal), float(dropout[0]),
+         int(dropout[1]) & 0xFFFFFFFFFFFFFFFF, int(dropout[2]))
     return out, lse
 
 
@@ -111,7 +113,8 @@ def has_native_bwd() -> bool:
     return lib is not None and hasattr(lib, "sb_attention_bwd")
 
 
-def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, scale: float, key_qend=None):
+def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, scale: float, key_qend=None,
+                  dropout=(0.0, 0, 0)):
     T, heads, d = q.shape
     kvh = k.shape[1]
     dq = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
@@ -120,21 +123,22 @@ def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, sca
     delta = _bwd_scratch(q.device, T, heads)
     call("sb_attention_bwd_ex", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
          ptr(seg_start), ptr(seg_end), ptr(key_qend), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
-         launches=3)
+         float(dropout[0]), int(dropout[1]) & 0xFFFFFFFFFFFFFFFF, int(dropout[2]), launches=3)
     return dq, dk, dv
 
 
 class AttentionFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, cu_seqlens, max_seqlen, causal, scale, window):
+    def forward(ctx, q, k, v, cu_seqlens, max_seqlen, causal, scale, window, dropout=(0.0, 0, 0)):
         if window:
             seg_start, seg_end, key_qend = window_bounds(cu_seqlens, q.shape[0], causal, int(window))
         else:
             seg_start, seg_end = segment_bounds(cu_seqlens, q.shape[0])
             key_qend = None
-        out, lse = attention_fwd(q, k, v, seg_start, seg_end, causal, scale)
+        out, lse = attention_fwd(q, k, v, seg_start, seg_end, causal, scale, dropout)
         ctx.save_for_backward(q, k, v, out, lse, seg_start, seg_end, cu_seqlens)
         ctx.key_qend = key_qend
+        ctx.dropout = dropout
         ctx.args = (max_seqlen, causal, scale, window)
         return out
 
@@ -146,8 +150,8 @@ class AttentionFn(torch.autograd.Function):
         impl = _BWD_IMPL
         if impl == "auto":
             impl = "sm100" if has_native_bwd() else "flash"
-        if impl == "sm100":
-            dq, dk, dv = attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal, scale, ctx.key_qend)
+        if impl == "sm100" or ctx.dropout[0] > 0.0:
+            dq, dk, dv = attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal, scale, ctx.key_qend, ctx.dropout)
         else:
             # library backward on this kernel's forward results (same LSE convention: natural log, [heads, tokens])
             from flash_attn.flash_attn_interface import _flash_attn_varlen_backward
@@ -158,7 +162,7 @@ class AttentionFn(torch.autograd.Function):
             w = (-1, -1) if not window else (int(window), 0 if causal else int(window))
             _flash_attn_varlen_backward(dout, qc, kc, vc, out, lse, dq, dk, dv, cu32, cu32, max_seqlen, max_seqlen, 0.0,
                                         scale, causal, w[0], w[1], 0.0, None, False, None)
-        return dq, dk, dv, None, None, None, None, None
+        return (dq, dk, dv) + (None,) * (len(ctx.needs_input_grad) - 3)
 
 
 def _decode_forward(q, k, v, causal, scale, window):
@@ -173,7 +177,7 @@ def _decode_forward(q, k, v, causal, scale, window):
     return out
 
 
-def sm100_attention(q, k, v, cu_seqlens, max_seqlen, causal, scale, window=None, cu_seqlens_k=None):
+def sm100_attention(q, k, v, cu_seqlens, max_seqlen, causal, scale, window=None, cu_seqlens_k=None, dropout=(0.0, 0, 0)):
     d = q.shape[-1]
     if d < 128:  # the kernel's tiles are 128 wide: zero columns change neither the scores nor the first d outputs
         pad = (0, 128 - d)
@@ -182,5 +186,5 @@ def sm100_attention(q, k, v, cu_seqlens, max_seqlen, causal, scale, window=None,
     if cu_seqlens_k is not None and cu_seqlens_k is not cu_seqlens:
         out = _decode_forward(q, k, v, causal, scale, window)
     else:
-        out = AttentionFn.apply(q, k, v, cu_seqlens, max_seqlen, causal, scale, window or None)
+        out = AttentionFn.apply(q, k, v, cu_seqlens, max_seqlen, causal, scale, window or None, tuple(dropout))
     return out[..., :d] if d < 128 else out

@@ -348,6 +348,29 @@ def test_lora_fused_projections_match_separate_lora_linears(tmp_path, mp):
         assert abs(x - y) / abs(y) < 2e-2, (fused, plain)
 
 
+@pytest.mark.parametrize("sp", [False, True])
+def test_tp2_loss_and_gradient_norm_match_tp1_from_the_same_checkpoint(tmp_path, sp):
+    """Gradient parity across layouts on the peer-memory kernels: a TP=1 run writes a checkpoint; TP=1 and TP=2 (fused
+    all-reduce, or sequence parallel with gated gathers / fused reduce-scatters) resume from it on the same data.  The
+    first step's loss and GLOBAL GRADIENT NORM (every gradient of the model, before any update) must agree."""
+    prefix = tmp_path / "d" / "tokens"
+    write_dataset(prefix, n_docs=1024, vocab=512)
+    a = {"vocab_size": 512, "hidden_size": 512, "num_attention_heads": 4, "attention_num_kv_heads": 2,
+         "sequence_length": 512, "precision": "bfloat16", "masked_softmax": {"kernel": "flash_attention"}}
+    ckpt = tmp_path / "ckpt"
+    base = dict(iters=1, gas=2, arch=a, learning_rate_scheduler={"learning_rate": 1e-4, "learning_rate_decay_style": "constant"})
+    dist_launcher(_zero_worker, world_size=1, timeout=400, fused=True,
+                  config_dict=tiny_config(prefix, trainer={"save_dir": str(ckpt), "save_interval": 1}, **base))
+    load = {"load_dir": str(ckpt), "load_optimizer_states": False, "load_context": False, "assert_checkpoint_loaded": True}
+    base["iters"] = 2
+    one = dist_launcher(_zero_worker, world_size=1, timeout=400, fused=True, config_dict=tiny_config(prefix, trainer=load, **base))[0]
+    two = dist_launcher(_zero_worker, world_size=2, timeout=400, fused=True,
+                        config_dict=tiny_config(prefix, mp=2, trainer=load, topology={"sequence_parallel": sp}, **base))[0]
+    (l1, g1), (l2, g2) = one[0], two[0]
+    assert abs(l1 - l2) / abs(l1) < 2e-3, (one, two)
+    assert abs(g1 - g2) / abs(g1) < 2e-2, (one, two)
+
+
 def test_sequence_parallel_fused_reduce_scatter_matches_nccl(tmp_path):
     """Sequence-parallel TP=2 training with the row-parallel reduce-scatters inside the GEMM launch against the same
     run on NCCL reduce-scatters."""

@@ -114,7 +114,7 @@ def test_gemm_swiglu(K, M, F, K_):
 
 @pytest.mark.parametrize("rms", [True, False])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("rows,cols", [(64, 256), (1000, 4096), (7, 8192)])
+@pytest.mark.parametrize("rows,cols", [(64, 256), (1000, 4096), (7, 8192), (33, 12288)])
 def test_norm_fwd_bwd(K, rms, dtype, rows, cols):
     torch.manual_seed(3)
     x = torch.randn(rows, cols, device="cuda", dtype=dtype)
@@ -514,3 +514,55 @@ def test_attention_sm100_kv_cache_decoding(tq, tk, window):
         out = attention(q, k, v, cu_q, tq, causal=True, scale=scale, cu_seqlens_k=cu_k, max_seqlen_k=tk, window=window)
         ref = attention_dense(q.float(), k.float(), v.float(), cu_q, cu_k, True, scale, window)
     assert _rel_err(out, ref) < 2e-2, _rel_err(out, ref)
+
+
+def _dropout_keep_mask(seed: int, p: float, heads: int, T: int, head_offset: int = 0) -> torch.Tensor:
+    """[heads, T, T] bool: the kernel's stateless keep decision (csrc/attention_sm100.cu: make_drop / drop_keep)."""
+    M = 0xFFFFFFFF
+    s32 = ((((seed ^ (seed >> 32)) & M) * 0x9E3779B1) + 0x7F4A7C15) & M
+    thr = max(1, int(p * 4294967296.0))
+    q = torch.arange(T, dtype=torch.int64, device="cuda").view(1, T, 1)
+    k = torch.arange(T, dtype=torch.int64, device="cuda").view(1, 1, T)
+    h = (torch.arange(heads, dtype=torch.int64, device="cuda") + head_offset).view(heads, 1, 1)
+    x = (q * 0x9E3779B1 + k * 0x85EBCA77 + h * 0xC2B2AE3D + s32) & M
+    x = x ^ (x >> 16)
+    x = (x * 0x7FEB352D) & M
+    x = x ^ (x >> 15)
+    x = (x * 0x846CA68B) & M
+    x = x ^ (x >> 16)
+    return x >= thr
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T,cu,heads,kv_heads", [(512, [0, 512], 4, 2), (777, [0, 300, 777], 4, 1)])
+def test_attention_sm100_dropout_matches_the_same_mask_in_fp32(causal, T, cu, heads, kv_heads):
+    """Attention-probability dropout: forward, dK/dV blocks and dQ blocks regenerate one and the same mask.  The oracle
+    applies that mask (rebuilt from the hash in Python) to the fp32 softmax; the keep rate must be about 1 - p."""
+    from scaling_b200.ops.attention import dense_mask, repeat_kv
+    from scaling_b200.ops.attention_sm100 import AttentionFn
+
+    torch.manual_seed(14)
+    dev, d, p, seed, hoff = "cuda", 128, 0.2, 0x1234ABCD5678, 3
+    q = torch.randn(T, heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(T, kv_heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(T, kv_heads, d, device=dev, dtype=torch.bfloat16, requires_grad=True)
+    cu_t = torch.tensor(cu, device=dev, dtype=torch.int32)
+    scale = 1.0 / math.sqrt(d)
+    out = AttentionFn.apply(q, k, v, cu_t, T, causal, scale, None, (p, seed, hoff))
+    keep = _dropout_keep_mask(seed, p, heads, T, hoff)
+    assert abs(float(keep.float().mean()) - (1 - p)) < 5e-3
+    qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    kk, vv = repeat_kv(kf, heads // kv_heads), repeat_kv(vf, heads // kv_heads)
+    scores = torch.einsum("qhd,khd->hqk", qf, kk) * scale
+    probs = torch.softmax(scores.masked_fill(dense_mask(cu_t, T, cu_t, T, causal, None)[None], float("-inf")), dim=-1)
+    ref = torch.einsum("hqk,khd->qhd", torch.nan_to_num(probs) * keep / (1 - p), vv)
+    assert _rel_err(out, ref) < 2e-2, _rel_err(out, ref)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    ref.backward(dout.float())
+    for name, g, r in (("dq", q.grad, qf.grad), ("dk", k.grad, kf.grad), ("dv", v.grad, vf.grad)):
+        assert _rel_err(g, r) < 3e-2, (name, _rel_err(g, r))
+    # p = 0 goes through the same entry point and equals the plain kernel bit for bit
+    a = AttentionFn.apply(q.detach(), k.detach(), v.detach(), cu_t, T, causal, scale, None, (0.0, seed, hoff))
+    b = AttentionFn.apply(q.detach(), k.detach(), v.detach(), cu_t, T, causal, scale, None)
+    assert torch.equal(a, b)
