@@ -29,7 +29,7 @@ constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
 constexpr uint32_t kPeerMask = 0xFEFFFFFF;  // clears the CTA-rank bit of a shared::cluster address -> leader's copy
 
-enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, kXentStats = 4 };
+enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, kXentStats = 4, kAct = 5 };
 
 // ---- fused all-reduce (kAllReduce) ----------------------------------------------------------------------------
 // One launch computes this rank's partial product AND the tensor-parallel sum of it.  Every rank owns a symmetric
@@ -794,6 +794,53 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         if (row_ok && n0 < p.N)
           reinterpret_cast<float4*>(p.aux)[(size_t)row * p.tiles_n + tn] =
               make_float4(m_run, s_run, 0.f, __int_as_float(best_i));
+      } else if (kEpi == kAct) {
+        // adapter / GELU-MLP up-projection: D = act(A·Bᵀ + bias) with the activation on the accumulator
+        // registers; the bf16 pre-activation goes to aux for the backward pass.  swiglu_up_row_offset carries the
+        // activation kind (0 GELU, 1 SiLU) for this epilogue.
+        const int n0 = tn * BN;
+        __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd;
+        __nv_bfloat16* arow = p.aux ? reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux : nullptr;
+        const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+        const bool silu = p.swiglu_up_row_offset != 0;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c, v);
+          tmem_ld_wait();
+          if (split) split_reduce_chunk<32>(v, p, sched, w, rank, row_in_cta, c);
+          const int col = n0 + c;
+          if (!row_ok || col >= p.N) continue;
+          const int nv = min(32, p.N - col);
+          uint32_t pre[16], act[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x0 = __uint_as_float(v[2 * i]), x1 = __uint_as_float(v[2 * i + 1]);
+            if (bias) {
+              if (2 * i < nv) x0 += __bfloat162float(bias[col + 2 * i]);
+              if (2 * i + 1 < nv) x1 += __bfloat162float(bias[col + 2 * i + 1]);
+            }
+            pre[i] = pack_bf16(x0, x1);
+            const float2 r = unpack_bf16(pre[i]);  // the activation sees what the backward pass will see
+            act[i] = silu ? pack_bf16(silu_f(r.x), silu_f(r.y)) : pack_bf16(gelu_f(r.x), gelu_f(r.y));
+          }
+          if (nv == 32) {
+            uint4* dst = reinterpret_cast<uint4*>(drow + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(act[4 * i], act[4 * i + 1], act[4 * i + 2], act[4 * i + 3]);
+            if (arow) {
+              uint4* ap = reinterpret_cast<uint4*>(arow + col);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) ap[i] = make_uint4(pre[4 * i], pre[4 * i + 1], pre[4 * i + 2], pre[4 * i + 3]);
+            }
+          } else {
+            for (int i = 0; i < nv; ++i) {
+              const float2 a2 = unpack_bf16(act[i >> 1]), p2 = unpack_bf16(pre[i >> 1]);
+              drow[col + i] = __float2bfloat16((i & 1) ? a2.y : a2.x);
+              if (arow) arow[col + i] = __float2bfloat16((i & 1) ? p2.y : p2.x);
+            }
+          }
+        }
       } else if (kEpi == kSwiGLU) {
         const int n0 = tn * (BN / 2);
         __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd;
@@ -1195,6 +1242,23 @@ extern "C" int sb_gemm2_xent_stats_bf16(const void* X, const void* W, void* logi
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + BN - 1) / BN;
   return launch<0, 0, kXentStats, __nv_bfloat16>(m, p, stream, max_ctas);
+}
+
+// Linear + activation in one launch (adapter bottlenecks, GELU / SiLU MLP up-projections):
+// H[M,N] = act(X·Wᵀ + bias), pre[M,N] (optional) = the bf16 pre-activation for the backward pass.  act: 0 GELU (erf),
+// 1 SiLU.  Reference: F.linear followed by torch.nn.functional.gelu / silu (core/nn/mlp.py:77-89,
+// transformer/model/layers/layer.py:143-186).
+extern "C" int sb_gemm2_act_bf16(const void* X, const void* W, const void* bias, void* H, void* pre, int M, int N, int K,
+                                 int ldx, int ldw, int ldh, int ldpre, int act, int max_ctas, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  Params p{};
+  Maps m;
+  if (int rc = make_maps(m, X, W, M, N, K, ldx, ldw, 0, 0, nullptr, p)) return rc;
+  p.M = M, p.N = N, p.K = K, p.D = H, p.ldd = ldh, p.bias = bias, p.aux = pre, p.ldaux = ldpre;
+  p.swiglu_up_row_offset = act;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + BN - 1) / BN;
+  return launch<0, 0, kAct, __nv_bfloat16>(m, p, stream, max_ctas);
 }
 
 // Same contract as sb_gemm_swiglu_bf16: CTA 0 of the pair stages the gate rows, CTA 1 the up rows of the tile.

@@ -62,9 +62,17 @@ class ParallelMLP(torch.nn.Module):
                                            init_method=init_method, parallel_input=True, parallel_output=True,
                                            bitfit_bias_name=bitfit_bias_name)
         self.activation_function = get_activation_function(activation_function)
+        self.activation_name = ActivationFunction(activation_function).value
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        h = self.activation_function(self.dense_in(x))
+        h = None
+        if x.is_cuda:
+            # up-projection with bias + activation in the GEMM epilogue (one launch instead of GEMM, bias add, activation)
+            comm = get_tp_comm(self.topology)
+            xin = x if (comm is not None or _sp(self.topology)) else copy_to_tensor_model_parallel_region(x, self.topology)
+            h = OF.linear_act(xin, self.dense_in.weight, self.dense_in.get_bias(), self.activation_name, comm=comm)
+        if h is None:
+            h = self.activation_function(self.dense_in(x))
         return _row_parallel_out(self.dense_out, h, self.topology)
 
 

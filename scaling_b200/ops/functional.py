@@ -576,6 +576,50 @@ class _ActFn(torch.autograd.Function):
         return K.act_bwd(x, dy.contiguous(), ctx.silu), None
 
 
+class _LinearActFn(torch.autograd.Function):
+    """act(x·Wᵀ + b) with the activation in the GEMM epilogue (adapter bottlenecks, GELU / SiLU MLP up-projections,
+    SURVEY §8 L2; reference: F.linear then gelu, core/nn/mlp.py:77-89).  Keeps the bf16 pre-activation for backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, silu, comm):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        h, pre = K.gemm_act(x2, weight, bias, silu)
+        ctx.save_for_backward(x2, weight, pre)
+        ctx.meta = (silu, comm, shape, bias is not None)
+        return h.view(*shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dh):
+        x2, weight, pre = ctx.saved_tensors
+        silu, comm, shape, has_bias = ctx.meta
+        dh2 = dh.reshape(-1, dh.shape[-1])
+        if not dh2.is_contiguous():
+            dh2 = dh2.contiguous()
+        dpre = K.act_bwd(pre, dh2, silu)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = (_gemm_nn_reduce(dpre, weight, comm) if comm is not None else _gemm_nn(dpre, weight)).view(shape)
+        if ctx.needs_input_grad[1]:
+            dw = _accumulate_wgrad(dpre, x2, weight)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = dpre.sum(0)
+        return dx, dw, db, None, None
+
+
+def linear_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], name: str, comm=None) -> Optional[torch.Tensor]:
+    """Fused column-parallel linear + activation, or None when the epilogue kernel does not apply.  ``comm``: sum dX over
+    the TP group inside the dgrad GEMM (replicated input)."""
+    m = x.numel() // x.shape[-1] if x.numel() else 0
+    if not (native_enabled(x) and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and m >= 256
+            and weight.shape[0] >= 128 and _aligned(*weight.shape) and _PLAIN_GEMM == "native" and name in ("gelu", "silu")
+            and (bias is None or bias.dtype == torch.bfloat16)):
+        return None
+    return _LinearActFn.apply(x, weight, bias, name == "silu", comm)
+
+
 def activation(x: torch.Tensor, name: str) -> torch.Tensor:
     if native_enabled(x) and x.dtype == torch.bfloat16 and x.numel() % 2 == 0 and x.numel() > 0:
         return _ActFn.apply(x, name == "silu")

@@ -231,6 +231,23 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True)
     return h, pre
 
 
+def gemm_act(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], silu: bool) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(act(x·Wᵀ + bias), pre-activation) in ONE launch of the 2-CTA GEMM (activation in the TMEM epilogue)."""
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 2 and w.dim() == 2
+    M, Kd = x.shape
+    N = w.shape[0]
+    assert w.shape[1] == Kd and M >= 256 and N >= 128 and gemm_supported(M, N, Kd, x.stride(0), w.stride(0), N)
+    assert x.stride(1) == 1 and w.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    h = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    pre = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    _ensure_split_workspace(x.device)
+    call("sb_gemm2_act_bf16", ptr(x), ptr(w), ptr(bias), ptr(h), ptr(pre), M, N, Kd, x.stride(0), w.stride(0), N, N,
+         int(silu), 0)
+    return h, pre
+
+
 # ----------------------------------------------------------------------------------------------------------- norms
 def norm_fwd(
     x: torch.Tensor,

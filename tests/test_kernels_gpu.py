@@ -566,3 +566,28 @@ def test_attention_sm100_dropout_matches_the_same_mask_in_fp32(causal, T, cu, he
     a = AttentionFn.apply(q.detach(), k.detach(), v.detach(), cu_t, T, causal, scale, None, (0.0, seed, hoff))
     b = AttentionFn.apply(q.detach(), k.detach(), v.detach(), cu_t, T, causal, scale, None)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("name", ["gelu", "silu"])
+@pytest.mark.parametrize("M,N,K_,bias", [(1024, 1024, 512, True), (1000, 520, 264, False), (4096, 1024, 4096, True)])
+def test_linear_with_activation_in_the_epilogue(name, M, N, K_, bias):
+    """act(x Wᵀ + b) from one GEMM launch (adapter / GELU-MLP up-projection) and its gradients vs torch autograd."""
+    from scaling_b200.ops import functional as OF
+
+    torch.manual_seed(2)
+    x = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    w = (torch.randn(N, K_, device="cuda") / math.sqrt(K_)).bfloat16().requires_grad_(True)
+    b = torch.randn(N, device="cuda").bfloat16().requires_grad_(True) if bias else None
+    y = OF.linear_act(x, w, b, name)
+    assert y is not None
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, wf = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    bf = b.detach().float().requires_grad_(True) if bias else None
+    act = torch.nn.functional.gelu if name == "gelu" else torch.nn.functional.silu
+    ref = act(torch.nn.functional.linear(xf, wf, bf))
+    ref.backward(dy.float())
+    assert _rel_err(y, ref) < 2e-2 and _max_rel_per_row(y, ref) < 5e-2, (_rel_err(y, ref), _max_rel_per_row(y, ref))
+    assert _rel_err(x.grad, xf.grad) < 3e-2 and _rel_err(w.grad, wf.grad) < 3e-2
+    if bias:
+        assert _rel_err(b.grad, bf.grad) < 3e-2
