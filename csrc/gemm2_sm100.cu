@@ -29,7 +29,7 @@ constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
 constexpr uint32_t kPeerMask = 0xFEFFFFFF;  // clears the CTA-rank bit of a shared::cluster address -> leader's copy
 
-enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, kXentStats = 4, kAct = 5 };
+enum Epilogue : int { kStore = 0, kAccumulate = 1, kSwiGLU = 2, kAllReduce = 3, kXentStats = 4, kAct = 5, kRope = 6 };
 
 // ---- fused all-reduce (kAllReduce) ----------------------------------------------------------------------------
 // One launch computes this rank's partial product AND the tensor-parallel sum of it.  Every rank owns a symmetric
@@ -65,6 +65,11 @@ struct Params {
   // gate[tm] has reached gate_target, so tiles of the local shard start at once and remote tiles as they land.
   const uint32_t* gate;
   uint32_t gate_target;
+  // kRope: rotary embedding (interleaved pairs) on the first rope_cols output columns, in the accumulator registers
+  const float* rope_cos;  // [positions, rope_rot / 2]
+  const float* rope_sin;
+  const int* rope_pos;    // [M] position of every row, or null: row % rope_seq
+  int rope_seq, rope_cols, rope_head_dim, rope_rot;
   // split-K tail: the last, partial wave of tiles is cut along K into `split` parts so that it fills the machine
   int full_tiles;   // tiles [0, full_tiles) run whole; the remaining `num_tiles - full_tiles` are split
   int split;        // parts per tail tile (1 = no splitting)
@@ -794,6 +799,52 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         if (row_ok && n0 < p.N)
           reinterpret_cast<float4*>(p.aux)[(size_t)row * p.tiles_n + tn] =
               make_float4(m_run, s_run, 0.f, __int_as_float(best_i));
+      } else if (kEpi == kRope) {
+        // q|k|v projection with the rotary embedding applied to the q and k columns while the row is in registers
+        // (fp32, one rounding) — the separate rotary pass over [T, q|k] disappears from the forward (SURVEY §8 A1;
+        // reference core/nn/rotary.py:68-90 after core/nn/attention/attention.py:509-566).
+        const int n0 = tn * BN;
+        __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.ldd;
+        const int half = p.rope_rot / 2;
+        const int rpos = row_ok ? (p.rope_pos ? __ldg(p.rope_pos + row) : row % p.rope_seq) : 0;
+        const float* cr = p.rope_cos + (size_t)rpos * half;
+        const float* sr = p.rope_sin + (size_t)rpos * half;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c, v);
+          tmem_ld_wait();
+          if (split) split_reduce_chunk<32>(v, p, sched, w, rank, row_in_cta, c);
+          const int col = n0 + c;
+          if (!row_ok || col >= p.N) continue;
+          const int d0 = col % p.rope_head_dim;  // head_dim % 32 == 0: a chunk never straddles heads
+          if (col < p.rope_cols && d0 < p.rope_rot) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {  // 4 groups of 4 pairs; rope_rot % 8 == 0 keeps a group inside or outside
+              if (d0 + 8 * g >= p.rope_rot) break;
+              const float4 c4 = __ldg(reinterpret_cast<const float4*>(cr + d0 / 2 + 4 * g));
+              const float4 s4 = __ldg(reinterpret_cast<const float4*>(sr + d0 / 2 + 4 * g));
+              const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float a = __uint_as_float(v[8 * g + 2 * k]), b = __uint_as_float(v[8 * g + 2 * k + 1]);
+                v[8 * g + 2 * k] = __float_as_uint(a * cc[k] - b * ss[k]);
+                v[8 * g + 2 * k + 1] = __float_as_uint(a * ss[k] + b * cc[k]);
+              }
+            }
+          }
+          if (col + 32 <= p.N) {
+            uint4* dst = reinterpret_cast<uint4*>(drow + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              dst[i] = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                                  pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                                  pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                                  pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
+          } else {
+            for (int i = 0; i < 32 && col + i < p.N; ++i) drow[col + i] = __float2bfloat16(__uint_as_float(v[i]));
+          }
+        }
       } else if (kEpi == kAct) {
         // adapter / GELU-MLP up-projection: D = act(A·Bᵀ + bias) with the activation on the accumulator
         // registers; the bf16 pre-activation goes to aux for the backward pass.  swiglu_up_row_offset carries the
@@ -1242,6 +1293,25 @@ extern "C" int sb_gemm2_xent_stats_bf16(const void* X, const void* W, void* logi
   p.tiles_m = (M + BM - 1) / BM;
   p.tiles_n = (N + BN - 1) / BN;
   return launch<0, 0, kXentStats, __nv_bfloat16>(m, p, stream, max_ctas);
+}
+
+// q|k|v projection + rotary in one launch: Y[M,N] = X·Wᵀ with the rotary embedding (interleaved pairs, "rotary_complex")
+// applied to columns [0, rope_cols) — heads of head_dim columns, the first rot_dim of each rotated — using
+// cos/sin[pos][rot_dim/2] fp32 tables and pos[M] (or row % seq when pos is NULL).  head_dim % 32 == 0, rot_dim % 8 == 0.
+extern "C" int sb_gemm2_rope_bf16(const void* X, const void* W, void* Y, int M, int N, int K, int ldx, int ldw, int ldy,
+                                  const float* cos_t, const float* sin_t, const int* pos, int seq, int rope_cols,
+                                  int head_dim, int rot_dim, int max_ctas, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if (head_dim % 32 || rot_dim % 8 || rot_dim > head_dim || rope_cols % head_dim || rope_cols > N || seq <= 0) return -1;
+  Params p{};
+  Maps m;
+  if (int rc = make_maps(m, X, W, M, N, K, ldx, ldw, 0, 0, nullptr, p)) return rc;
+  p.M = M, p.N = N, p.K = K, p.D = Y, p.ldd = ldy;
+  p.rope_cos = cos_t, p.rope_sin = sin_t, p.rope_pos = pos, p.rope_seq = seq, p.rope_cols = rope_cols;
+  p.rope_head_dim = head_dim, p.rope_rot = rot_dim;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + BN - 1) / BN;
+  return launch<0, 0, kRope, __nv_bfloat16>(m, p, stream, max_ctas);
 }
 
 // Linear + activation in one launch (adapter bottlenecks, GELU / SiLU MLP up-projections):

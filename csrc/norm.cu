@@ -263,7 +263,7 @@ static int fwd(const void* x, const void* res, const void* w, const void* b, voi
   if (cols % 8) return -1;
   size_t smem = (size_t)cols * 4;
   auto k = rms ? norm_fwd_kernel<T, true> : norm_fwd_kernel<T, false>;
-  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 1024 > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k<<<rows, kThreads, smem, st>>>((const T*)x, (const T*)res, (const T*)w, (const T*)b, (T*)y, (T*)sum_out, mean, rstd,
                                  rows, cols, eps);
   return (int)cudaGetLastError();
@@ -277,7 +277,7 @@ static int bwd(const void* dy, const void* x, const void* w, const float* mean, 
   const int grid = grid_for(rows);
   size_t smem = (size_t)cols * 4 * (rms ? 1 : 2);
   auto k = rms ? norm_bwd_kernel<T, true> : norm_bwd_kernel<T, false>;
-  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 1024 > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   float* pw = scratch;
   float* pb = scratch + (size_t)grid * cols;
   k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,
@@ -384,7 +384,7 @@ static int bwd_noalloc(const void* dy, const void* x, const void* w, const float
   if (int rc = noalloc_scratch(&scratch)) return rc;
   size_t smem = (size_t)cols * 4 * (rms ? 1 : 2);
   auto k = rms ? norm_bwd_kernel<T, true> : norm_bwd_kernel<T, false>;
-  if (smem > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 1024 > 48 * 1024) SB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   float* pw = scratch;
   float* pb = scratch + (size_t)grid * cols;
   k<<<grid, kThreads, smem, st>>>((const T*)dy, (const T*)x, (const T*)w, mean, rstd, (const T*)dres, (T*)dx, pw, pb,

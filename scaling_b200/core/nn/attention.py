@@ -207,22 +207,31 @@ class ParallelSelfAttention(torch.nn.Module):
         weights = (self.query.weight, self.key.weight, self.value.weight)
         if not OF.qkv_rope_fusable(x, d, rot.dimensions) or OF.fused_view(tuple(w.data for w in weights)) is None:
             return None
+        n_out = sum(w.shape[0] for w in weights)
+        pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
+        tp = 1 if self.topology is None else self.topology.config.model_parallel_size
+        s_full = x.shape[1] * (tp if sp_shard else 1)
+        # rotary in the GEMM epilogue (q and k columns rotated while the accumulator row is in registers)
+        in_gemm = OF.rope_in_gemm_supported(x, n_out, d, rot.dimensions, rot.mode)
+        rope = (rot.cos_table, rot.sin_table, pos, s_full, (nh + nkv) * d, d, rot.dimensions) if in_gemm else None
         if sp_shard:
             sp_comm = get_tp_comm(self.topology, sequence_parallel=True)
-            if not OF.sp_gather_fusable(x, sp_comm, sum(w.shape[0] for w in weights)):
+            if not OF.sp_gather_fusable(x, sp_comm, n_out):
                 return None
-            y = OF.multi_linear_fused(x, weights, sp=sp_comm)  # all-gather(seq) inside the GEMM: y is [b, s, ΣN]
+            y = OF.multi_linear_fused(x, weights, sp=sp_comm, rope=rope)  # all-gather(seq) inside the GEMM: [b, s, ΣN]
             if y is None:
                 return None
-            s = y.shape[1]
-            pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
-            return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s, rot.mode, rot.dimensions)
+            return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s_full, rot.mode, rot.dimensions,
+                                     pre_rotated=in_gemm)
         comm = get_tp_comm(self.topology) if x.is_cuda else None
         if comm is None and not self._sp():
             x = copy_to_tensor_model_parallel_region(x, self.topology)
-        y = OF.multi_linear_fused(x, weights, comm=comm)
+        y = OF.multi_linear_fused(x, weights, comm=comm, rope=rope)
         if y is None:
             return None
+        if in_gemm:
+            return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s_full, rot.mode, rot.dimensions,
+                                     pre_rotated=True)
         s = x.shape[1]
         pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
         return OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s, rot.mode, rot.dimensions)

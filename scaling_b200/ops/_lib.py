@@ -29,6 +29,7 @@ _SIGS = {
                               c_int, c_int, P],
     "sb_gemm2_allreduce_lowrank_bf16": [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                         c_int, P, P, c_int, c_int, c_uint, c_ulonglong, c_uint, c_int, P],
+    "sb_gemm2_rope_bf16": [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P, P, P, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_act_bf16": [P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_allreduce_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int,

@@ -322,23 +322,30 @@ class _MultiLinearFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, fused_w, fused_main_grad, comm, sp, *weights):
+    def forward(ctx, x, fused_w, fused_main_grad, comm, sp, rope, *weights):
         shape = x.shape
         ctx.sp = sp
+
+        def project(a2):  # plain GEMM, or (q|k|v) GEMM with the rotary embedding in its epilogue
+            if rope is None:
+                return K.gemm(a2, fused_w) if sp is not None else _gemm_nt(a2, fused_w)
+            cos, sin, pos, seq, rope_cols, d, rot_dim = rope
+            return K.gemm_rope(a2, fused_w, cos, sin, pos, seq, rope_cols, d, rot_dim)
+
         if sp is not None:
             # sequence parallel: x is this rank's [b, s/tp, h] shard.  all-gather -> GEMM as one unit: the
             # shard is pushed into every rank's gather buffer and the GEMM's TMA producer starts each 256-row tile when
             # its rows have arrived; only the SHARD is kept for backward.
             xl = x.contiguous()
             xg = K.seq_gather_gated(xl, sp)
-            y = K.gemm(xg.view(-1, shape[-1]), fused_w)
+            y = project(xg.view(-1, shape[-1]))
             ctx.save_for_backward(xl, fused_w)
             shape = xg.shape
         else:
             x2 = x.reshape(-1, shape[-1])
             if not x2.is_contiguous():
                 x2 = x2.contiguous()
-            y = _gemm_nt(x2, fused_w)
+            y = project(x2)
             ctx.save_for_backward(x2, fused_w)
         ctx.comm = comm
         ctx.fused_main_grad = fused_main_grad
@@ -358,20 +365,20 @@ class _MultiLinearFn(torch.autograd.Function):
             seq = dy.shape[1]
             if ctx.needs_input_grad[0]:
                 dx = K.gemm_reduce_scatter(dy2, fused_w, ctx.sp, seq, b_mn=True).view(ctx.x_shape)
-            if any(ctx.needs_input_grad[5:]):
+            if any(ctx.needs_input_grad[6:]):
                 x2 = K.seq_all_gather(x2, ctx.sp, clone=False).view(-1, x2.shape[-1])
         elif ctx.needs_input_grad[0]:
             dx = _gemm_nn_reduce(dy2, fused_w, ctx.comm) if ctx.comm is not None else _gemm_nn(dy2, fused_w)
             dx = dx.view(ctx.x_shape)
         grads: list = [None] * len(ctx.sizes)
-        if not any(ctx.needs_input_grad[5:]):
+        if not any(ctx.needs_input_grad[6:]):
             pass  # frozen weights: no wgrad GEMM at all
         elif ctx.fused_main_grad is not None:
             K.gemm(dy2, x2, a_mn=True, b_mn=True, out=ctx.fused_main_grad, accumulate=True)
         else:
             dw = K.gemm(dy2, x2, a_mn=True, b_mn=True, out_dtype=fused_w.dtype)
             grads = list(dw.split(ctx.sizes, dim=0))
-        return (dx, None, None, None, None, *grads)
+        return (dx, None, None, None, None, None, *grads)
 
 
 def fused_view(tensors: Tuple[torch.Tensor, ...]) -> Optional[torch.Tensor]:
@@ -401,16 +408,18 @@ def sp_gather_fusable(x_local: torch.Tensor, sp_comm, n_out: int) -> bool:
             and K.seq_gather_gated_supported(x_local, sp_comm) and n_out >= 128)
 
 
-def multi_linear_fused(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None, sp=None) -> Optional[torch.Tensor]:
+def multi_linear_fused(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=None, sp=None, rope=None) -> Optional[torch.Tensor]:
     """x·[W_0; W_1; …]ᵀ as one [..., ΣN_i] tensor when the weights are adjacent in the arena (see multi_linear), else None.
-    ``sp``: x is a sequence-parallel shard [b, s/tp, h]; it is all-gathered INTO the GEMM (result is [b, s, ΣN_i])."""
+    ``sp``: x is a sequence-parallel shard [b, s/tp, h]; it is all-gathered INTO the GEMM (result is [b, s, ΣN_i]).
+    ``rope`` = (cos, sin, pos, seq, rope_cols, head_dim, rot_dim): rotary embedding on the first rope_cols output
+    columns in the GEMM epilogue (see :func:`rope_in_gemm_supported`)."""
     if native_enabled(x) and x.dtype == torch.bfloat16 and all(_aligned(*w.shape) for w in weights) and x.numel() > 0:
         fw = fused_view(tuple(w.data for w in weights))
         if fw is not None:
             mains = [getattr(w, "main_grad", None) for w in weights]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                return _MultiLinearFn.apply(x, fw, fmg, comm, sp, *weights)
+                return _MultiLinearFn.apply(x, fw, fmg, comm, sp, rope, *weights)
     return None
 
 
@@ -423,7 +432,7 @@ def multi_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], comm=
             mains = [getattr(w, "main_grad", None) for w in weights]
             fmg = fused_view(tuple(mains)) if all(m is not None for m in mains) else None
             if fmg is not None or all(m is None for m in mains):
-                y = _MultiLinearFn.apply(x, fw, fmg, comm, None, *weights)
+                y = _MultiLinearFn.apply(x, fw, fmg, comm, None, None, *weights)
                 return tuple(y.split([w.shape[0] for w in weights], dim=-1))
     if comm is not None:
         x = _CopyToRegion.apply(x, comm)
@@ -658,11 +667,13 @@ class _QKVRopeFn(torch.autograd.Function):
     rotary launches and a cat backward (reference: rotary after separate projections, attention.py:560-600)."""
 
     @staticmethod
-    def forward(ctx, y, cos, sin, pos, seq, mode, rot_dim, nh, nkv, d):
+    def forward(ctx, y, cos, sin, pos, seq, mode, rot_dim, nh, nkv, d, pre_rotated=False):
         T = y.shape[0]
         ctx.save_for_backward(cos, sin, pos)
         ctx.args = (seq, mode, rot_dim, nh, nkv, d, y.shape)
         y2 = y.reshape(T, -1)
+        if pre_rotated:  # the projection GEMM's epilogue already rotated q and k: the split is three strided views
+            return _qkv_views(y2, nh, nkv, d)
         out = torch.empty((T, nh + 2 * nkv, d), dtype=y.dtype, device=y.device)
         ins = _qkv_views(y2, nh, nkv, d)
         outs = (out[:, :nh], out[:, nh:nh + nkv], out[:, nh + nkv:])
@@ -678,7 +689,7 @@ class _QKVRopeFn(torch.autograd.Function):
         ins = tuple(g if (g.stride(2) == 1 and g.stride(1) == d) else g.contiguous() for g in (dq, dk, dv))
         K.qkv_rope(ins, _qkv_views(dy, nh, nkv, d), (nh, nkv, nkv), (True, True, False), cos, sin, pos, seq, mode,
                    rot_dim, backward=True)
-        return dy.view(shape), None, None, None, None, None, None, None, None, None
+        return (dy.view(shape),) + (None,) * (len(ctx.needs_input_grad) - 1)
 
 
 def _qkv_views(y2: torch.Tensor, nh: int, nkv: int, d: int):
@@ -690,9 +701,19 @@ def _qkv_views(y2: torch.Tensor, nh: int, nkv: int, d: int):
 
 
 def qkv_rope_split(y: torch.Tensor, nh: int, nkv: int, d: int, cos: torch.Tensor, sin: torch.Tensor,
-                   pos: Optional[torch.Tensor], seq: int, mode: int, rot_dim: int):
-    """y: [..., (nh + 2·nkv)·d] fused projection output → (q [T, nh, d], k [T, nkv, d], v [T, nkv, d]), q and k rotated."""
-    return _QKVRopeFn.apply(y.reshape(-1, y.shape[-1]), cos, sin, pos, seq, mode, rot_dim, nh, nkv, d)
+                   pos: Optional[torch.Tensor], seq: int, mode: int, rot_dim: int, pre_rotated: bool = False):
+    """y: [..., (nh + 2·nkv)·d] fused projection output → (q [T, nh, d], k [T, nkv, d], v [T, nkv, d]), q and k rotated.
+    ``pre_rotated``: the GEMM that produced y already applied the rotation (``rope=`` of :func:`multi_linear_fused`); the
+    forward is then free (strided views), the backward still un-rotates dq / dk while assembling the fused dY."""
+    return _QKVRopeFn.apply(y.reshape(-1, y.shape[-1]), cos, sin, pos, seq, mode, rot_dim, nh, nkv, d, pre_rotated)
+
+
+def rope_in_gemm_supported(x: torch.Tensor, n_out: int, d: int, rot_dim: int, mode: int) -> bool:
+    m = x.numel() // x.shape[-1] if x.numel() else 0
+    return _PLAIN_GEMM == "native" and _ROPE_IN_GEMM and K.gemm_rope_supported(m, n_out, d, rot_dim, mode)
+
+
+_ROPE_IN_GEMM = os.environ.get("SCALING_B200_ROPE_IN_GEMM", "0") == "1"  # opt-in until measured on the GPU
 
 
 def qkv_rope_fusable(x: torch.Tensor, d: int, rot_dim: int) -> bool:

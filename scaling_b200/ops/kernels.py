@@ -231,6 +231,28 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, keep_pre: bool = True)
     return h, pre
 
 
+def gemm_rope_supported(M: int, N: int, d: int, rot_dim: int, mode: int) -> bool:
+    return _GEMM_IMPL == "2cta" and mode == 0 and M >= 256 and N >= 128 and d % 32 == 0 and rot_dim % 8 == 0 and 0 < rot_dim <= d
+
+
+def gemm_rope(x: torch.Tensor, w: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: Optional[torch.Tensor], seq: int,
+              rope_cols: int, d: int, rot_dim: int) -> torch.Tensor:
+    """Y = x·Wᵀ with the rotary embedding (interleaved pairs) applied to the first ``rope_cols`` columns (q and k heads of
+    ``d`` columns each) in the GEMM epilogue."""
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 2 and w.dim() == 2
+    M, Kd = x.shape
+    N = w.shape[0]
+    assert w.shape[1] == Kd and x.stride(1) == 1 and w.stride(1) == 1 and gemm_supported(M, N, Kd, x.stride(0), w.stride(0), N)
+    assert cos.dtype == torch.float32 and sin.dtype == torch.float32 and cos.is_contiguous() and sin.is_contiguous()
+    assert pos is None or (pos.dtype == torch.int32 and pos.is_contiguous() and pos.numel() == M)
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    _ensure_split_workspace(x.device)
+    _apply_gate(x, "sb_gemm2_rope_bf16")
+    call("sb_gemm2_rope_bf16", ptr(x), ptr(w), ptr(y), M, N, Kd, x.stride(0), w.stride(0), N, ptr(cos), ptr(sin), ptr(pos),
+         seq, rope_cols, d, rot_dim, 0)
+    return y
+
+
 def gemm_act(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], silu: bool) -> Tuple[torch.Tensor, torch.Tensor]:
     """(act(x·Wᵀ + bias), pre-activation) in ONE launch of the 2-CTA GEMM (activation in the TMEM epilogue)."""
     assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 2 and w.dim() == 2

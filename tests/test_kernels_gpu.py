@@ -591,3 +591,34 @@ def test_linear_with_activation_in_the_epilogue(name, M, N, K_, bias):
     assert _rel_err(x.grad, xf.grad) < 3e-2 and _rel_err(w.grad, wf.grad) < 3e-2
     if bias:
         assert _rel_err(b.grad, bf.grad) < 3e-2
+
+
+@pytest.mark.parametrize("M,nh,nkv,K_,rot", [(4096, 32, 8, 4096, 128), (1000, 4, 2, 520, 64), (512, 16, 4, 1024, 128)])
+@pytest.mark.parametrize("with_pos", [False, True])
+def test_qkv_gemm_with_rotary_in_the_epilogue(M, nh, nkv, K_, rot, with_pos):
+    """q|k|v projection with the rotary embedding applied in the GEMM epilogue against GEMM followed by the rotary kernel
+    (and against the fp32 expression): q and k columns rotated, v columns untouched."""
+    from scaling_b200.ops import kernels as K
+
+    torch.manual_seed(6)
+    d, seq = 128, 256
+    N = (nh + 2 * nkv) * d
+    x = torch.randn(M, K_, device="cuda", dtype=torch.bfloat16)
+    w = (torch.randn(N, K_, device="cuda") / math.sqrt(K_)).bfloat16()
+    inv = 1.0 / (10000 ** (torch.arange(0, rot, 2, device="cuda").float() / rot))
+    ang = torch.arange(seq, device="cuda").float()[:, None] * inv[None]
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    pos = torch.randint(0, seq, (M,), device="cuda", dtype=torch.int32) if with_pos else None
+    y = K.gemm_rope(x, w, cos, sin, pos, seq, (nh + nkv) * d, d, rot)
+    ref = (x.float() @ w.float().t()).view(M, nh + 2 * nkv, d)
+    p = (pos.long() if with_pos else torch.arange(M, device="cuda") % seq)
+    c, s = cos[p][:, None, :], sin[p][:, None, :]
+    a, b = ref[:, :nh + nkv, 0:rot:2].clone(), ref[:, :nh + nkv, 1:rot:2].clone()
+    ref[:, :nh + nkv, 0:rot:2] = a * c - b * s
+    ref[:, :nh + nkv, 1:rot:2] = a * s + b * c
+    ref = ref.view(M, N)
+    assert _rel_err(y, ref) < 1e-2 and _max_rel_per_row(y, ref) < 3e-2, (_rel_err(y, ref), _max_rel_per_row(y, ref))
+    # the unfused pair of kernels agrees as well
+    y2 = K.gemm(x, w)
+    K.rope_(y2.view(M, nh + 2 * nkv, d)[:, :nh + nkv], cos, sin, pos, seq, 0, rot)
+    assert _rel_err(y, y2) < 1e-2
