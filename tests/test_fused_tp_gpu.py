@@ -96,8 +96,9 @@ def test_gemm_reduce_scatter_kernel(world):
 
 
 def _stress_worker(rank: int, world_size: int, master_port: int, iters: int):
-    """Signal/wait protocol under skew: ranks are delayed by random amounts before (and between) launches, shapes and
-    layouts change from call to call, and results are checked against NCCL every time.  A lost flag, a stale-parity
+    """Signal/wait protocols under skew (fused all-reduce, reduce-scatter tile owners, arrival-gated all-gather -> GEMM):
+    ranks are delayed by random amounts before (and between) launches, shapes, layouts and collectives change from call to
+    call, and results are checked against NCCL.  A lost flag, a stale-parity
     read or a premature buffer reuse shows up as a mismatch or as the kernel's 30 s watchdog trap."""
     import random
 
@@ -128,10 +129,28 @@ def _stress_worker(rank: int, world_size: int, master_port: int, iters: int):
         a, b, want = data[shape]
         if jitter.random() < 0.5:
             torch.cuda._sleep(int(jitter.random() * 3_000_000))  # up to ~2 ms of device-side skew
-        out = K.gemm_allreduce(a, b, comm, b_mn=shape[3])
-        if i % 8 == 0 or i > iters - 4:
-            err = ((out.float() - want).abs().max() / want.abs().max()).item()
-            assert err < 2e-2, (i, shape, err)
+        M = shape[0]
+        seq = M // 2 if (M // 2) % (256 * world_size) == 0 else (M if M % (256 * world_size) == 0 else 0)
+        mode = order.random()  # same choice on every rank: all-reduce, reduce-scatter or gated all-gather -> GEMM
+        if mode < 0.3 and seq:
+            # reduce-scatter flavour of the same kernel (tile owners): this rank's sequence slice of the sum
+            out = K.gemm_reduce_scatter(a, b, comm, seq, b_mn=shape[3])
+            sl = seq // world_size
+            ref = want.view(M // seq, seq, -1)[:, rank * sl:(rank + 1) * sl].reshape(out.shape)
+        elif mode < 0.5 and M % (256 * world_size) == 0 and not shape[3] and shape[1] >= 128:
+            # all-gather -> GEMM: every rank contributes a row shard of A, the gated producer consumes it as it lands
+            shard = a.view(1, M, -1)[:, rank * (M // world_size):(rank + 1) * (M // world_size)].contiguous()
+            gathered = K.seq_gather_gated(shard, comm)
+            out = K.gemm(gathered.view(M, -1), b, out_dtype=torch.float32)
+            parts = [torch.empty_like(shard) for _ in range(world_size)]
+            dist.all_gather(parts, shard)
+            ref = torch.cat(parts, dim=1).view(M, -1).float() @ b.float().t()
+        else:
+            out = K.gemm_allreduce(a, b, comm, b_mn=shape[3])
+            ref = want
+        if i % 8 == 0 or i > iters - 4 or mode < 0.5:
+            err = ((out.float() - ref).abs().max() / ref.abs().max()).item()
+            assert err < 2e-2, (i, shape, mode, err)
             worst = max(worst, err)
     torch.cuda.synchronize()
     return worst
