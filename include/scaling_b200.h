@@ -139,10 +139,14 @@ int sb_attention_fwd(const void* q, const void* k, const void* v, void* out, flo
                      long long v_pitch, float scale, int causal, cudaStream_t st);
 /* Generalised key side: k, v hold Tk rows (KV-cache decoding, Tk != T needs causal == 0) and with causal == 0 the arrays
  * are per-row KEY bounds "row t attends to keys [seg_start[t], seg_end[t])", non-decreasing in t: causal, right-aligned
- * causal, sliding windows (reference attention.py:242-257, 571-592, 599-667) are all just bounds. */
+ * causal, sliding windows (reference attention.py:242-257, 571-592, 599-667) are all just bounds.
+ * dropout_p > 0 drops attention probabilities with a stateless hash of (dropout_seed, head_offset + head, q row, key):
+ * forward and backward regenerate the same mask, nothing is stored; head_offset is the first global head of a
+ * tensor-parallel shard so every shard draws its own stream. */
 int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
                         const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch, long long k_pitch,
-                        long long v_pitch, float scale, int causal, cudaStream_t st);
+                        long long v_pitch, float scale, int causal, float dropout_p, unsigned long long dropout_seed,
+                        int head_offset, cudaStream_t st);
 int sb_attention_bwd_pitch(int T);
 long long sb_attention_bwd_scratch_floats(int T, int heads);
 int sb_attention_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
@@ -154,7 +158,8 @@ int sb_attention_bwd(const void* dout, const void* q, const void* k, const void*
 int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
                         float* scratch, void* dq, void* dk, void* dv, const int* seg_start, const int* seg_end,
                         const int* key_qend, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
-                        long long v_pitch, float scale, int causal, cudaStream_t st);
+                        long long v_pitch, float scale, int causal, float dropout_p, unsigned long long dropout_seed,
+                        int head_offset, cudaStream_t st);
 
 /* Bind `device`'s primary context to the calling thread (tensor-map encoding is a driver call and needs one; PyTorch's
  * autograd worker threads set their device lazily). */

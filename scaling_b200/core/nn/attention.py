@@ -268,9 +268,10 @@ class ParallelSelfAttention(torch.nn.Module):
             return (1, 0, None)
         return (t.config.model_parallel_size, t.model_parallel_rank, t.model_parallel_group)
 
-    def _project_qkv_lora(self, x: torch.Tensor):
+    def _project_qkv_lora(self, x: torch.Tensor, position_ids: Optional[torch.Tensor] = None):
         """q/k/v with their LoRA updates inside the projection GEMMs (low-rank K-slab, OF.lora_linear); None when the
-        fused form does not apply (then: plain projections + separate LoRA linears)."""
+        fused form does not apply (then: plain projections + separate LoRA linears).  Returns (q, k, v, rotated):
+        ``rotated`` says that the rotary embedding has already been applied (split + rotate kernel of the fast path)."""
         if not self._lora_fusable() or not x.is_cuda or any(
                 m.get_bias() is not None for m in (self.query, self.key, self.value)):
             return None
@@ -279,6 +280,22 @@ class ParallelSelfAttention(torch.nn.Module):
         nh, nkv, d = self.num_attention_heads_per_partition, self.num_kv_heads_per_partition, self.head_dim
         comm = get_tp_comm(self.topology)
         tp = self._tp_triple()
+        name = self.lora_config.name
+        mods = [self.lora_modules[f"{kind}_{name}"] if f"{kind}_{name}" in self.lora_modules else None
+                for kind in ("query", "key", "value")]
+        if all(m is not None for m in mods) and len({m.scaling for m in mods}) == 1:
+            # frozen, adjacent base weights: q|k|v and their three LoRA pairs as one low-rank GEMM (one dX reduction)
+            y = OF.qkv_lora_linear(x, (self.query.weight, self.key.weight, self.value.weight),
+                                   tuple((m.dense_in.weight, m.dense_out.weight) for m in mods), mods[0].scaling, tp, comm)
+            if y is not None:
+                rot = self.rotary_embedding
+                if rot is not None and not self.key_query_norm and \
+                        OF.qkv_rope_fusable(x, d, rot.dimensions):
+                    pos = None if position_ids is None else position_ids.reshape(-1).to(torch.int32).contiguous()
+                    return (*OF.qkv_rope_split(y, nh, nkv, d, rot.cos_table, rot.sin_table, pos, s, rot.mode,
+                                               rot.dimensions), True)
+                q, k, v = y.split([nh * d, nkv * d, nkv * d], dim=-1)
+                return q.reshape(T, nh, d), k.reshape(T, nkv, d), v.reshape(T, nkv, d), False
         outs = []
         for kind, base, heads in (("query", self.query, nh), ("key", self.key, nkv), ("value", self.value, nkv)):
             mod = self.lora_modules[f"{kind}_{self.lora_config.name}"] if f"{kind}_{self.lora_config.name}" in self.lora_modules else None
@@ -290,7 +307,7 @@ class ParallelSelfAttention(torch.nn.Module):
             else:
                 y = base(x)
             outs.append(y.reshape(T, heads, d))
-        return tuple(outs)
+        return (*outs, False)
 
     def forward(self, x: torch.Tensor, cumulative_seq_lengths: Optional[torch.Tensor],
                 position_ids: Optional[torch.Tensor], cumulative_seq_lengths_key: Optional[torch.Tensor] = None,
@@ -315,9 +332,10 @@ class ParallelSelfAttention(torch.nn.Module):
         if fused is not None:
             q, k, v = fused
         else:
-            lora_fused = self._project_qkv_lora(x)
+            lora_fused = self._project_qkv_lora(x, position_ids)
+            rotated = False
             if lora_fused is not None:
-                q, k, v = lora_fused
+                q, k, v, rotated = lora_fused
             else:
                 q, k, v = self._project_qkv(x)
                 if self.lora_config is not None and not self.lora_merged_state:
@@ -328,7 +346,7 @@ class ParallelSelfAttention(torch.nn.Module):
                 q = self.norm_query(q, gather=False)
                 k = self.norm_key(k, gather=False)
 
-            if self.rotary_embedding is not None:
+            if self.rotary_embedding is not None and not rotated:
                 pos = None if position_ids is None else position_ids.reshape(-1)
                 q = self.rotary_embedding.apply_packed(q, pos, s)
                 k = self.rotary_embedding.apply_packed(k, pos, s)

@@ -28,6 +28,13 @@ from .loss_scaler import LossScaler
 from .param_group import OptimizerParamGroup
 
 
+def _weights_changed() -> None:
+    """The arena kernels rewrite parameters without autograd noticing: drop per-step caches derived from weights."""
+    from ...ops.functional import bump_weight_epoch
+
+    bump_weight_epoch()
+
+
 class OptimizerStepOutput(NamedTuple):
     global_grad_norm: Optional[float]
     global_grad_norm_clipped: Optional[float]
@@ -175,6 +182,7 @@ class Optimizer(BaseOptimizer):
 
     def step(self) -> OptimizerStepOutput:
         self.step_index += 1
+        _weights_changed()
         topo = self.topology
         c = self.config
         for g in self.parameter_groups:
@@ -238,6 +246,7 @@ class Optimizer(BaseOptimizer):
                                    ls.current_loss_scale, debug)
 
     def refresh_optimizer_after_model_change(self) -> None:
+        _weights_changed()
         for g in self.parameter_groups:
             g.refresh_optimized_params(self.topology)
 
@@ -337,5 +346,6 @@ class Optimizer(BaseOptimizer):
                 g.scatter_full_state(g.master, o, split_parameter(entry["parameter"], m, topo).reshape(-1).to(dev))
                 g.scatter_full_state(g.exp_avg, o, split_parameter(entry["optimizer_state"]["exp_avg"], m, topo).reshape(-1).to(dev))
                 g.scatter_full_state(g.exp_avg_sq, o, split_parameter(entry["optimizer_state"]["exp_avg_sq"], m, topo).reshape(-1).to(dev))
+        _weights_changed()
         if not loaded_any:
             logger.warning(f"no optimizer checkpoint files found in {directory}")

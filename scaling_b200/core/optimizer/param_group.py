@@ -50,6 +50,36 @@ def flatten_dense_tensors_aligned(tensor_list: List[torch.Tensor], alignment: in
     return flat, padded - total
 
 
+def pack_frozen_parameters(parameters: List[torch.Tensor]) -> List[torch.Tensor]:
+    """Move parameters that no optimizer group owns (finetuning: the frozen base weights) into one flat arena per
+    (device, dtype) with the trained arenas' layout — registration order, ``ALIGN``-element slots.  The layers' fused
+    forms (q|k|v as one GEMM, gate|up dual GEMM) take adjacent weights as one zero-copy [ΣN, K] view; without this a
+    frozen model would fall back to one GEMM per projection.  ``p.data`` become views, values are kept; parameters
+    are moved one at a time so the peak extra memory is one arena, not a second copy of the model.  Returns the arenas."""
+    by_kind: Dict[Tuple[torch.device, torch.dtype], List[torch.Tensor]] = {}
+    seen: set = set()
+    for p in parameters:
+        if id(p) in seen or p.requires_grad or p.numel() == 0:
+            continue
+        seen.add(id(p))
+        by_kind.setdefault((p.device, p.dtype), []).append(p)
+    arenas = []
+    for (device, dtype), plist in by_kind.items():
+        if len(plist) < 2:
+            continue
+        total = sum(_round_up(p.numel(), ALIGN) for p in plist)
+        arena = torch.zeros(total, dtype=dtype, device=device)
+        off = 0
+        for p in plist:
+            n = p.numel()
+            view = arena[off:off + n].view(p.shape)
+            view.copy_(p.data)
+            p.data = view
+            off += _round_up(n, ALIGN)
+        arenas.append(arena)
+    return arenas
+
+
 def get_data_parallel_partitions(tensor: torch.Tensor, topology: Topology) -> List[torch.Tensor]:
     dp = topology.config.data_parallel_size
     assert tensor.numel() % dp == 0

@@ -210,6 +210,35 @@ def _gather_dim(t: torch.Tensor, dim: int, tp) -> torch.Tensor:
     return torch.cat(list(parts.unbind(0)), dim=dim).contiguous()
 
 
+_WEIGHT_EPOCH = 0
+_ROW_LORA_CACHE: dict = {}
+
+
+def bump_weight_epoch() -> None:
+    """Called by whoever rewrites parameters behind autograd's back (the optimizer's arena kernels): invalidates
+    per-step caches derived from weights."""
+    global _WEIGHT_EPOCH
+    _WEIGHT_EPOCH += 1
+
+
+def _row_lora_operands(A: torch.Tensor, B: torch.Tensor, tp, kl: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Row-parallel LoRA needs this rank's COLUMNS of the full A and the full B; both are gathered over the TP group.
+    The pair only changes at an optimizer step, so the gathers run once per step, not once per micro-batch."""
+    size, rank, _ = tp
+    if size == 1:
+        return A[:, :kl], B
+    key = (A.data_ptr(), B.data_ptr(), kl)
+    stamp = (_WEIGHT_EPOCH, A._version, B._version)
+    hit = _ROW_LORA_CACHE.get(key)
+    if hit is not None and hit[0] == stamp:
+        return hit[1], hit[2]
+    with torch.no_grad():
+        a_cols = _gather_dim(A, 0, tp)[:, rank * kl:(rank + 1) * kl].contiguous()
+        b_full = _gather_dim(B, 1, tp)
+    _ROW_LORA_CACHE[key] = (stamp, a_cols, b_full)
+    return a_cols, b_full
+
+
 class _LoraLinearFn(torch.autograd.Function):
     """y = x·Wᵀ + s·(x·Aᵀ)·Bᵀ with the low-rank pair riding as an extra K-slab of the base GEMM, forward AND backward
     (reference core/nn/lora.py:103-112 runs two extra linears and an add, and for the attention output
@@ -235,9 +264,7 @@ class _LoraLinearFn(torch.autograd.Function):
             y = K.gemm_lowrank(x2, W, ts, B)
             ctx.save_for_backward(x2, W, A, B, ts)
         else:
-            kl = x2.shape[1]
-            a_cols = _gather_dim(A, 0, tp)[:, rank * kl:(rank + 1) * kl].contiguous()  # [r, K/tp]
-            b_full = _gather_dim(B, 1, tp)  # [N, r]
+            a_cols, b_full = _row_lora_operands(A, B, tp, x2.shape[1])  # [r, K/tp], [N, r]
             ts = K.gemm(x2, a_cols) * scale  # this rank's partial of the rank activations
             if size > 1 and comm is not None:
                 y = K.gemm_lowrank(x2, W, ts, b_full, comm=comm)
@@ -309,6 +336,36 @@ def lora_linear(x: torch.Tensor, W: torch.Tensor, A: torch.Tensor, B: torch.Tens
             and r_full % 8 == 0 and _PLAIN_GEMM == "native"):
         return None
     return _LoraLinearFn.apply(x, W, A, B, float(scale), kind, tp, comm)
+
+
+def qkv_lora_linear(x: torch.Tensor, weights: Tuple[torch.nn.Parameter, ...], loras: Tuple[Tuple[torch.Tensor, torch.Tensor], ...],
+                    scale: float, tp=(1, 0, None), comm=None) -> Optional[torch.Tensor]:
+    """q|k|v with a LoRA pair on every projection as ONE low-rank GEMM each way: [x | t]·[W_q;W_k;W_v | blockdiag(B)]ᵀ
+    where t = x·[A_q;A_k;A_v]ᵀ.  Needs frozen base weights that are adjacent in memory (pack_frozen_parameters);
+    then forward is one rank GEMM + one fused GEMM and backward ONE dX GEMM with ONE (fused) TP reduction instead of
+    three of each, at the price of the block-diagonal's zero blocks (3r of K + 3r columns).  Returns [..., ΣN] or None.
+
+    ``loras[i] = (A_i [r/tp, K], B_i [N_i(/tp), r])``; the gathered rank activations are rank-major
+    ``[rank0: q k v | rank1: q k v | …]``, so block i of B is spread over the matching columns of every rank's group."""
+    size = tp[0]
+    if any(w.requires_grad for w in weights) or len({a.shape for a, _ in loras}) != 1:
+        return None
+    fw = fused_view(tuple(w.data for w in weights))
+    m = x.numel() // x.shape[-1] if x.numel() else 0
+    rl = loras[0][0].shape[0]  # r / tp
+    n = len(loras)
+    if fw is None or not (native_enabled(x) and x.dtype == fw.dtype == torch.bfloat16 and m >= 256 and fw.shape[0] >= 128
+                          and _aligned(*fw.shape) and rl % 8 == 0 and _PLAIN_GEMM == "native"
+                          and all(a.dtype == b.dtype == torch.bfloat16 and b.shape[1] == rl * size for a, b in loras)):
+        return None
+    a_cat = torch.cat([a for a, _ in loras], dim=0)  # [n·r/tp, K]
+    blocks = []
+    for i, (_, b) in enumerate(loras):
+        own = b.reshape(b.shape[0], size, 1, rl)
+        zero = own.new_zeros(own.shape)
+        blocks.append(torch.cat([own if j == i else zero for j in range(n)], dim=2))  # [N_i, tp, n, r/tp]
+    b_bd = torch.cat(blocks, dim=0).reshape(fw.shape[0], size * n * rl)
+    return _LoraLinearFn.apply(x, fw, a_cat, b_bd, float(scale), "column", tp, comm)
 
 
 # ------------------------------------------------------------------------------------------------ fused q|k|v etc.

@@ -32,6 +32,24 @@ _ENABLED = os.environ.get("SCALING_B200_FUSED_TP", "1") == "1"
 _FLAG_ALIGN = 1024
 
 
+def _enable_symm_mem(group_name: str) -> None:
+    """Older torch builds need the group registered for symmetric memory before the first rendezvous; newer ones
+    register every group themselves and only warn about the call."""
+    import warnings
+
+    import torch.distributed._symmetric_memory as symm_mem
+
+    fn = getattr(symm_mem, "enable_symm_mem_for_group", None)
+    if fn is None:
+        return
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", FutureWarning)
+        try:
+            fn(group_name)
+        except Exception:  # noqa: BLE001  (already enabled / not required by this torch)
+            pass
+
+
 def fused_tp_enabled() -> bool:
     return _ENABLED
 
@@ -66,10 +84,7 @@ class TPComm:
 
         torch.cuda.synchronize(self.device)
         name = self.group.group_name
-        try:
-            symm_mem.enable_symm_mem_for_group(name)
-        except Exception:  # noqa: BLE001  (already enabled / not required by this torch)
-            pass
+        _enable_symm_mem(name)
         n = self.size
         slot_bytes = (slot_bytes + 65535) // 65536 * 65536
         flag_slot = (slot_bytes // 65536 * 4 + _FLAG_ALIGN - 1) // _FLAG_ALIGN * _FLAG_ALIGN
@@ -184,10 +199,7 @@ class GroupBarrier:
         import torch.distributed._symmetric_memory as symm_mem
 
         name = group.group_name
-        try:
-            symm_mem.enable_symm_mem_for_group(name)
-        except Exception:  # noqa: BLE001
-            pass
+        _enable_symm_mem(name)
         self._flags = symm_mem.empty(64, dtype=torch.int32, device=device)
         self._hdl = symm_mem.rendezvous(self._flags, name)
         self._flags.zero_()
@@ -219,10 +231,7 @@ class SymmetricArena:
         import torch.distributed._symmetric_memory as symm_mem
 
         name = group.group_name
-        try:
-            symm_mem.enable_symm_mem_for_group(name)
-        except Exception:  # noqa: BLE001
-            pass
+        _enable_symm_mem(name)
         self._buf = symm_mem.empty(numel, dtype=dtype, device=device)
         self._hdl = symm_mem.rendezvous(self._buf, name)
         self._buf.zero_()

@@ -177,6 +177,11 @@ def get_parameter_groups(context: TransformerContext, model: TransformerParallel
     for _, p, _ in named:
         if id(p) not in trained:
             p.requires_grad_(False)
+    if len(trained) < len(named):
+        # frozen weights get the trained arenas' layout, so the fused q|k|v / gate|up GEMMs keep applying to them
+        from ...core.optimizer.param_group import pack_frozen_parameters
+
+        model._frozen_arenas = pack_frozen_parameters([p for _, p, _ in named])  # type: ignore[attr-defined]
     groups: List[OptimizerParamGroup] = []
     c = counts.tolist()
     if c[0] > 0:

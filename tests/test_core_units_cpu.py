@@ -436,3 +436,27 @@ def test_tokenizer_wrapper(tmp_path):
     with_space, without = load_tokenizers(tmp_path / "vocab.json")
     assert with_space.encode("world") == [4] and without.encode("world") == [5]  # continuation pieces get no prefix space
     assert Tokenizer.from_str((tmp_path / "vocab.json").read_text()).encode("hello") == [2]
+
+
+def test_pack_frozen_parameters_keeps_values_and_makes_neighbours_adjacent():
+    """Frozen parameters move into one arena in registration order (128-element slots); trained ones are left alone."""
+    import torch
+
+    from scaling_b200.core.optimizer.param_group import pack_frozen_parameters
+    from scaling_b200.ops.functional import fused_view
+
+    torch.manual_seed(0)
+    a, b, c = (torch.nn.Parameter(torch.randn(n, 128), requires_grad=False) for n in (4, 2, 3))
+    t = torch.nn.Parameter(torch.randn(5, 128))
+    odd = torch.nn.Parameter(torch.randn(7), requires_grad=False)
+    before = [p.detach().clone() for p in (a, b, c, t, odd)]
+    ptr_t = t.data_ptr()
+    arenas = pack_frozen_parameters([a, b, t, c, odd, a])
+    assert len(arenas) == 1 and arenas[0].numel() == (4 + 2 + 3) * 128 + 128
+    for p, ref in zip((a, b, c, t, odd), before):
+        assert torch.equal(p.detach(), ref)
+    assert t.data_ptr() == ptr_t
+    fv = fused_view((a.data, b.data, c.data))
+    assert fv is not None and fv.shape == (9, 128) and torch.equal(fv[4:6], b.detach())
+    a.data.mul_(2.0)  # views, not copies
+    assert torch.equal(arenas[0][:4 * 128].view(4, 128), a.detach())

@@ -428,6 +428,39 @@ def test_lora_linear_matches_autograd_of_the_plain_expression(kind):
         assert g is not None and _rel_err(g, ref) < 2e-2, (name, _rel_err(g, ref))
 
 
+def test_qkv_lora_as_one_low_rank_gemm_matches_three_separate_projections():
+    """Frozen adjacent q|k|v weights + a LoRA pair on each: ONE fused GEMM each way (block-diagonal B) against torch
+    autograd of the three plain expressions, output and every gradient that exists (x, A_i, B_i)."""
+    from scaling_b200.core.optimizer.param_group import pack_frozen_parameters
+    from scaling_b200.ops import functional as OF
+
+    torch.manual_seed(3)
+    M, Kd, r, s = 1024, 1024, 32, 2.0
+    sizes = (1024, 256, 256)
+    x = torch.randn(2, M // 2, Kd, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    Ws = [torch.nn.Parameter((torch.randn(n, Kd, device="cuda") / math.sqrt(Kd)).bfloat16(), requires_grad=False) for n in sizes]
+    assert OF.fused_view(tuple(w.data for w in Ws)) is None  # separate allocations ...
+    pack_frozen_parameters(Ws)
+    assert OF.fused_view(tuple(w.data for w in Ws)) is not None  # ... adjacent after packing
+    As = [(torch.randn(r, Kd, device="cuda") / math.sqrt(Kd)).bfloat16().requires_grad_(True) for _ in sizes]
+    Bs = [(torch.randn(n, r, device="cuda") / math.sqrt(r)).bfloat16().requires_grad_(True) for n in sizes]
+    y = OF.qkv_lora_linear(x, tuple(Ws), tuple(zip(As, Bs)), s)
+    assert y is not None and y.shape == (2, M // 2, sum(sizes))
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf = x.detach().float().requires_grad_(True)
+    Af = [a.detach().float().requires_grad_(True) for a in As]
+    Bf = [b.detach().float().requires_grad_(True) for b in Bs]
+    yr = torch.cat([xf @ w.float().t() + s * (xf @ a.t()) @ b.t() for w, a, b in zip(Ws, Af, Bf)], dim=-1)
+    yr.backward(dy.float())
+    assert _rel_err(y.detach(), yr.detach()) < 2e-2
+    assert _rel_err(x.grad, xf.grad) < 2e-2
+    for i in range(3):
+        assert _rel_err(As[i].grad, Af[i].grad) < 2e-2, ("dA", i, _rel_err(As[i].grad, Af[i].grad))
+        assert _rel_err(Bs[i].grad, Bf[i].grad) < 2e-2, ("dB", i, _rel_err(Bs[i].grad, Bf[i].grad))
+    assert all(w.grad is None for w in Ws)
+
+
 @pytest.mark.parametrize("M,N,K_", [(4096, 32000, 1024), (512, 1000, 256), (1000, 16000, 512), (256, 128, 64)])
 def test_lm_head_gemm_with_cross_entropy_statistics_in_the_epilogue(M, N, K_):
     """Logits + per-tile CE statistics from ONE GEMM launch, merged by the combine / finalize kernels, against

@@ -15,6 +15,9 @@ p.add_argument("--ops", default="sm100")
 p.add_argument("--tag", default="ours")
 p.add_argument("--plain-gemm", default="native")
 p.add_argument("--attention", default="auto")
+p.add_argument("--preset", default="7b")
+p.add_argument("--layout", default=None, help="tp,pp,dp")
+p.add_argument("--sp", action="store_true")
 a = p.parse_args()
 
 from scaling_b200.core import LaunchConfig  # noqa: E402
@@ -28,7 +31,12 @@ ATT.set_attention_impl(a.attention)
 import os  # noqa: E402
 
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
-args = argparse.Namespace(gpus=world, steps=1, warmup=1, layers=a.layers, ops=a.ops, act_ckpt="disabled", seqs_per_gpu=4, layout=None)
+args = argparse.Namespace(gpus=world, steps=1, warmup=1, layers=a.layers, ops=a.ops, act_ckpt="disabled", seqs_per_gpu=4, layout=a.layout,
+                          preset=a.preset, sp=a.sp)
+if "layout" in bench.PRESETS[a.preset]:
+    bench.LAYOUTS[world] = bench.PRESETS[a.preset]["layout"](world)
+if a.layout:
+    bench.LAYOUTS[world] = tuple(int(v) for v in a.layout.split(","))
 prefix = Path("/tmp/scaling_prof") / "data"
 bench.write_synthetic_dataset(prefix, n_docs=64 * world, vocab=32000, rank=rank)
 cfg = bench.model_config(args, world, prefix)
