@@ -123,7 +123,7 @@ SB_DEVICE float fwd_row_max(uint32_t s_tmem, int kv0, int rs, int re) {
   return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
 }
 
-template <bool kMask, bool kDrop>
+template <bool kMask, bool kDrop, bool kHalf>
 SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scale_log2, float m_use, float& l0, float& l1,
                             const Drop& drop, int head, int row) {
 #pragma unroll 1
@@ -148,12 +148,14 @@ SB_DEVICE void fwd_exp_pack(uint32_t s_tmem, int kv0, int rs, int re, float scal
         a = drop_keep(drop, head, row, key) ? a * drop.inv_keep : 0.f;
         b = drop_keep(drop, head, row, key + 1) ? b * drop.inv_keep : 0.f;
       }
-      packed[i] = pack_bf16(a, b);
+      packed[i] = pack16<kHalf>(a, b);
     }
     tmem_st_32x32b_x16(s_tmem + c / 2, packed);
   }
 }
 
+// kHalf: q, k, v, out (and the probabilities fed back to the tensor core) are fp16 instead of bf16.
+template <bool kHalf>
 __global__ void __launch_bounds__(kThreads, 1)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                      const __grid_constant__ CUtensorMap map_v, const Params p) {
@@ -239,8 +241,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);  // Q, K both K-major
-      constexpr uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);    // P K-major (TMEM), V MN-major
+      constexpr uint32_t idesc_s = make_idesc_16(BQ, BKV, 0, 0, kHalf);  // Q, K both K-major
+      constexpr uint32_t idesc_o = make_idesc_16(BQ, D, 0, 1, kHalf);    // P K-major (TMEM), V MN-major
       auto issue_s = [&](int x, int j) {
         const uint32_t q_addr = smem_u32(sQ + x * kTileBytes);
         const uint32_t k_addr = smem_u32(sK + (j % kKStages) * kTileBytes);
@@ -325,13 +327,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
       float l0 = 0.f, l1 = 0.f;
       if (p.drop.thr) {
         if (need_mask)
-          fwd_exp_pack<true, true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+          fwd_exp_pack<true, true, kHalf>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
         else
-          fwd_exp_pack<false, true>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+          fwd_exp_pack<false, true, kHalf>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
       } else if (need_mask) {
-        fwd_exp_pack<true, false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+        fwd_exp_pack<true, false, kHalf>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
       } else {
-        fwd_exp_pack<false, false>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
+        fwd_exp_pack<false, false, kHalf>(s_tmem, kv0, rs, re, p.scale_log2, m_use, l0, l1, p.drop, head, row);
       }
       l += l0 + l1;
       tmem_st_wait();
@@ -379,10 +381,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_con
         uint4* dst = reinterpret_cast<uint4*>(orow + c);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          dst[i] = make_uint4(pack_bf16(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv),
-                              pack_bf16(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv),
-                              pack_bf16(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv),
-                              pack_bf16(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv));
+          dst[i] = make_uint4(pack16<kHalf>(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv),
+                              pack16<kHalf>(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv),
+                              pack16<kHalf>(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv),
+                              pack16<kHalf>(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv));
         }
       }
     }
@@ -447,10 +449,11 @@ extern "C" int sb_attention_fwd(const void* q, const void* k, const void* v, voi
   return sb_attention_fwd_ex(q, k, v, out, lse, seg_start, seg_end, T, T, heads, kv_heads, q_pitch, k_pitch, v_pitch, scale,
                              causal, 0.f, 0ull, 0, stream);
 }
-extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
-                                   const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
-                                   long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
-                                   unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+template <bool kHalf>
+static int attention_fwd_impl(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                              const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
+                              long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
+                              unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
   if (heads % kv_heads || Tk <= 0 || (causal && Tk != T) || dropout_p < 0.f || dropout_p >= 1.f) return -1;
@@ -464,10 +467,26 @@ extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, 
   p.drop = make_drop(dropout_p, dropout_seed, head_offset);
   static sb::PerDeviceOnce once;
   if (once.first())
-    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel<kHalf>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kSmemBytes));
   const int blocks = (T + 2 * BQ - 1) / (2 * BQ) * heads;
-  attention_fwd_kernel<<<blocks, kThreads, kSmemBytes, stream>>>(mq, mk, mv, p);
+  attention_fwd_kernel<kHalf><<<blocks, kThreads, kSmemBytes, stream>>>(mq, mk, mv, p);
   return (int)cudaGetLastError();
+}
+extern "C" int sb_attention_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                                   const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
+                                   long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
+                                   unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+  return attention_fwd_impl<false>(q, k, v, out, lse, seg_start, seg_end, T, Tk, heads, kv_heads, q_pitch, k_pitch, v_pitch,
+                                   scale, causal, dropout_p, dropout_seed, head_offset, stream);
+}
+// Same contract with fp16 tensors (the reference's fp16 + loss-scaler grid, tests/core/test_training/test_training.py).
+extern "C" int sb_attention_fwd_f16(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                                    const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch,
+                                    long long k_pitch, long long v_pitch, float scale, int causal, float dropout_p,
+                                    unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+  return attention_fwd_impl<true>(q, k, v, out, lse, seg_start, seg_end, T, Tk, heads, kv_heads, q_pitch, k_pitch, v_pitch,
+                                  scale, causal, dropout_p, dropout_seed, head_offset, stream);
 }
 
 // =================================================================================================================
@@ -531,6 +550,7 @@ SB_DEVICE void load_sub(uint8_t* dst, const CUtensorMap* map, uint64_t* bar, int
   tma_load_2d(dst + kSubBytes / 2, map, bar, col0 + 64, row0);
 }
 
+template <bool kHalf>
 __global__ void bwd_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
                                  const float* __restrict__ lse, float* __restrict__ lse2, float* __restrict__ delta, int T,
                                  int heads, int Tp) {
@@ -539,7 +559,7 @@ __global__ void bwd_delta_kernel(const __nv_bfloat16* __restrict__ dout, const _
   const int t = w / heads, h = w % heads;
   const uint2 a = *reinterpret_cast<const uint2*>(dout + (size_t)w * 128 + lane * 4);
   const uint2 b = *reinterpret_cast<const uint2*>(out + (size_t)w * 128 + lane * 4);
-  float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), b0 = unpack_bf16(b.x), b1 = unpack_bf16(b.y);
+  float2 a0 = unpack16<kHalf>(a.x), a1 = unpack16<kHalf>(a.y), b0 = unpack16<kHalf>(b.x), b1 = unpack16<kHalf>(b.y);
   float s = warp_sum(a0.x * b0.x + a0.y * b0.y + a1.x * b1.x + a1.y * b1.y);
   if (lane == 0) {
     delta[(size_t)h * Tp + t] = s;
@@ -547,7 +567,8 @@ __global__ void bwd_delta_kernel(const __nv_bfloat16* __restrict__ dout, const _
   }
 }
 
-SB_DEVICE void store_row_bf16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
+template <bool kHalf>
+SB_DEVICE void store_row_16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
 #pragma unroll 1
   for (int c = 0; c < 128; c += 32) {
     uint32_t v[32];
@@ -557,17 +578,17 @@ SB_DEVICE void store_row_bf16(__nv_bfloat16* dst, uint32_t tmem_addr, bool ok) {
       uint4* d = reinterpret_cast<uint4*>(dst + c);
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        d[i] = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
-                          pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
-                          pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
-                          pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
+        d[i] = make_uint4(pack16<kHalf>(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                          pack16<kHalf>(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                          pack16<kHalf>(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                          pack16<kHalf>(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------------- dK / dV
 
-template <bool kMask, bool kDrop>
+template <bool kMask, bool kDrop, bool kHalf>
 SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_lse2, const float* st_del, int qs0, int key,
                                    bool key_ok, const BwdParams& p, int head) {
 #pragma unroll 1
@@ -603,15 +624,16 @@ SB_DEVICE void dkdv_softmax_chunks(uint32_t t_s, uint32_t t_p, const float* st_l
         }
         ds[e] = pr * (dpe - dl[e]) * p.scale;
       }
-      pp[i] = pack_bf16(pv[0], pv[1]);
-      pp[i + 1] = pack_bf16(pv[2], pv[3]);
-      pd[i] = pack_bf16(ds[0], ds[1]);
-      pd[i + 1] = pack_bf16(ds[2], ds[3]);
+      pp[i] = pack16<kHalf>(pv[0], pv[1]);
+      pp[i + 1] = pack16<kHalf>(pv[2], pv[3]);
+      pd[i] = pack16<kHalf>(ds[0], ds[1]);
+      pd[i + 1] = pack16<kHalf>(ds[2], ds[3]);
     }
     tmem_st_32x32b_x16(t_s + c / 2, pp);  // P^T over the consumed S^T columns
     tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS^T over the consumed dP^T columns
   }
 }
+template <bool kHalf>
 SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do, const CUtensorMap& map_k,
                              const CUtensorMap& map_v, const BwdParams& p, const int kv_tile, const int kv_head) {
   extern __shared__ uint8_t smem_raw[];
@@ -686,8 +708,8 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc_t = make_idesc_bf16(128, BS, 0, 0);   // Sᵀ / dPᵀ: [128 keys, 64 queries]
-      constexpr uint32_t idesc_g = make_idesc_bf16(128, 128, 0, 1);  // dV / dK : A from TMEM, B MN-major
+      constexpr uint32_t idesc_t = make_idesc_16(128, BS, 0, 0, kHalf);   // Sᵀ / dPᵀ: [128 keys, 64 queries]
+      constexpr uint32_t idesc_g = make_idesc_16(128, 128, 0, 1, kHalf);  // dV / dK : A from TMEM, B MN-major
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
       auto issue_scores = [&](int it) {
         const int st = it % kRing;
@@ -747,13 +769,13 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
       const int hq = kvh * group + it / n_sub;  // query head of this sub-tile (for the dropout mask)
       if (p.drop.thr) {
         if (sub_mask[it % n_sub])
-          dkdv_softmax_chunks<true, true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+          dkdv_softmax_chunks<true, true, kHalf>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
         else
-          dkdv_softmax_chunks<false, true>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+          dkdv_softmax_chunks<false, true, kHalf>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
       } else if (sub_mask[it % n_sub]) {
-        dkdv_softmax_chunks<true, false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+        dkdv_softmax_chunks<true, false, kHalf>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
       } else {
-        dkdv_softmax_chunks<false, false>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
+        dkdv_softmax_chunks<false, false, kHalf>(t_s, t_p, st_lse2, st_del, qs0, key, key_ok, p, hq);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -765,7 +787,7 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
     tc_fence_after();
     __nv_bfloat16* dst = (wg == 0 ? p.dv : p.dk) + ((size_t)key * p.kv_heads + kvh) * D;
     if (n_it > 0) {
-      store_row_bf16(dst, tmem + lane_base + (wg == 0 ? kColdV : kColdK), key_ok);
+      store_row_16<kHalf>(dst, tmem + lane_base + (wg == 0 ? kColdV : kColdK), key_ok);
     } else if (key_ok) {
       for (int c = 0; c < D; c += 8) *reinterpret_cast<uint4*>(dst + c) = make_uint4(0, 0, 0, 0);
     }
@@ -780,7 +802,7 @@ SB_DEVICE void bwd_dkdv_body(const CUtensorMap& map_q, const CUtensorMap& map_do
 
 // ------------------------------------------------------------------------------------------------- dQ
 
-template <bool kMask, bool kDrop>
+template <bool kMask, bool kDrop, bool kHalf>
 SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, int re, float scale_log2, float lse2,
                                  float del, float scale, const Drop& drop, int head, int row) {
 #pragma unroll 1
@@ -804,11 +826,12 @@ SB_DEVICE void dq_softmax_chunks(uint32_t t_s, uint32_t t_p, int ks0, int rs, in
         if (kDrop) dpe = drop_keep(drop, head, row, ks0 + c + 2 * i + e) ? dpe * drop.inv_keep : 0.f;
         d2[e] = pr * (dpe - del) * scale;
       }
-      pd[i] = pack_bf16(d2[0], d2[1]);
+      pd[i] = pack16<kHalf>(d2[0], d2[1]);
     }
     tmem_st_32x32b_x16(t_p + c / 2, pd);  // dS over the consumed dP columns
   }
 }
+template <bool kHalf>
 SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, const CUtensorMap& map_k,
                            const CUtensorMap& map_v, const BwdParams& p, const int q_tile, const int q_head) {
   extern __shared__ uint8_t smem_raw[];
@@ -869,8 +892,8 @@ SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, 
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc_t = make_idesc_bf16(128, BS, 0, 0);   // S / dP: [128 queries, 64 keys]
-      constexpr uint32_t idesc_g = make_idesc_bf16(128, 128, 0, 1);  // dQ: A (dS) from TMEM, B (K_sub) MN-major
+      constexpr uint32_t idesc_t = make_idesc_16(128, BS, 0, 0, kHalf);   // S / dP: [128 queries, 64 keys]
+      constexpr uint32_t idesc_g = make_idesc_16(128, 128, 0, 1, kHalf);  // dQ: A (dS) from TMEM, B (K_sub) MN-major
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sdO);
       auto issue_scores = [&](int it) {
         const int st = it % kRing;
@@ -928,13 +951,13 @@ SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, 
       const uint32_t t_s = tmem + lane_base + (it & 1) * 128, t_p = t_s + 64;
       if (p.drop.thr) {
         if (need_mask)
-          dq_softmax_chunks<true, true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+          dq_softmax_chunks<true, true, kHalf>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
         else
-          dq_softmax_chunks<false, true>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+          dq_softmax_chunks<false, true, kHalf>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
       } else if (need_mask) {
-        dq_softmax_chunks<true, false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+        dq_softmax_chunks<true, false, kHalf>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
       } else {
-        dq_softmax_chunks<false, false>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
+        dq_softmax_chunks<false, false, kHalf>(t_s, t_p, ks0, rs, re, p.scale_log2, lse2, del, p.scale, p.drop, head, row);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -946,7 +969,7 @@ SB_DEVICE void bwd_dq_body(const CUtensorMap& map_q, const CUtensorMap& map_do, 
     if (wg == 0) {
       __nv_bfloat16* dst = p.dq + ((size_t)row * p.heads + head) * D;
       if (n_it > 0) {
-        store_row_bf16(dst, tmem + lane_base + kColdQ, row_ok);
+        store_row_16<kHalf>(dst, tmem + lane_base + kColdQ, row_ok);
       } else if (row_ok) {
         for (int c = 0; c < D; c += 8) *reinterpret_cast<uint4*>(dst + c) = make_uint4(0, 0, 0, 0);
       }
@@ -978,6 +1001,7 @@ static int make_map_box(CUtensorMap* m, const void* ptr, uint64_t width, uint64_
 // [n_dkdv, n_dkdv + n_dq) compute dQ of one (query tile, head).  Both sets are ordered heaviest first (causal: early key
 // tiles / late query tiles see the most partners), so the block scheduler packs the light dQ tiles into the holes the
 // long dK/dV tiles leave — with few heads per GPU (tensor parallel) the dK/dV grid alone is a single, badly balanced wave.
+template <bool kHalf>
 __global__ void __launch_bounds__(384, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap kv_map_q, const __grid_constant__ CUtensorMap kv_map_do,
                      const __grid_constant__ CUtensorMap kv_map_k, const __grid_constant__ CUtensorMap kv_map_v,
@@ -988,10 +1012,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap kv_map_q, const __grid_
   const int tiles = (p.T + 127) / 128;
   const int n_dkdv = tiles * p.kv_heads;
   if (b < n_dkdv) {
-    bwd_dkdv_body(kv_map_q, kv_map_do, kv_map_k, kv_map_v, p, b / p.kv_heads, b % p.kv_heads);
+    bwd_dkdv_body<kHalf>(kv_map_q, kv_map_do, kv_map_k, kv_map_v, p, b / p.kv_heads, b % p.kv_heads);
   } else {
     const int c = b - n_dkdv;
-    bwd_dq_body(q_map_q, q_map_do, q_map_k, q_map_v, p, tiles - 1 - c / p.heads, c % p.heads);
+    bwd_dq_body<kHalf>(q_map_q, q_map_do, q_map_k, q_map_v, p, tiles - 1 - c / p.heads, c % p.heads);
   }
 }
 
@@ -1024,11 +1048,12 @@ extern "C" int sb_attention_bwd(const void* dout, const void* q, const void* k, 
   return sb_attention_bwd_ex(dout, q, k, v, out, lse, scratch, dq, dk, dv, seg_start, seg_end, nullptr, T, heads, kv_heads,
                              q_pitch, k_pitch, v_pitch, scale, causal, 0.f, 0ull, 0, stream);
 }
-extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out,
-                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
-                                   const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
-                                   long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
-                                   float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+template <bool kHalf>
+static int attention_bwd_impl(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                              const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
+                              const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
+                              long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
+                              float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
   using namespace sb::attn;
   if (T <= 0) return 0;
   if (heads % kv_heads) return -1;
@@ -1036,8 +1061,8 @@ extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* 
   const int Tp = sb_attention_bwd_pitch(T);
   float* lse2 = scratch;
   float* delta = scratch + (size_t)heads * Tp;
-  bwd_delta_kernel<<<(T * heads * 32 + 255) / 256, 256, 0, stream>>>((const __nv_bfloat16*)dout, (const __nv_bfloat16*)out,
-                                                                      lse, lse2, delta, T, heads, Tp);
+  bwd_delta_kernel<kHalf><<<(T * heads * 32 + 255) / 256, 256, 0, stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, lse, lse2, delta, T, heads, Tp);
   BwdParams p;
   p.T = T, p.heads = heads, p.kv_heads = kv_heads, p.scale = scale, p.scale_log2 = scale * kLog2e, p.causal = causal;
   p.seg_start = seg_start, p.seg_end = seg_end, p.key_qend = key_qend, p.lse2 = lse2, p.delta = delta, p.Tp = Tp;
@@ -1046,7 +1071,8 @@ extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* 
   static sb::PerDeviceOnce once;
   static bool separate = false;  // SCALING_B200_ATTN_BWD_SEPARATE=1: two launches (dK/dV, then dQ), for A/B timing
   if (once.first()) {
-    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
+    SB_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel<kHalf>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kBwdSmemBytes));
     const char* e = getenv("SCALING_B200_ATTN_BWD_SEPARATE");
     separate = e && e[0] == '1';
   }
@@ -1063,10 +1089,28 @@ extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* 
   const int tiles = (T + 127) / 128;
   const int n_dkdv = tiles * kv_heads, n_dq = tiles * heads;
   if (separate) {
-    attention_bwd_kernel<<<n_dkdv, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
-    attention_bwd_kernel<<<n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, n_dkdv);
+    attention_bwd_kernel<kHalf><<<n_dkdv, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
+    attention_bwd_kernel<kHalf><<<n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, n_dkdv);
   } else {
-    attention_bwd_kernel<<<n_dkdv + n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
+    attention_bwd_kernel<kHalf><<<n_dkdv + n_dq, 384, kBwdSmemBytes, stream>>>(kq, kdo, kk, kv_, qq, qdo, qk, qv, p, 0);
   }
   return (int)cudaGetLastError();
+}
+extern "C" int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
+                                   const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
+                                   long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
+                                   float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+  return attention_bwd_impl<false>(dout, q, k, v, out, lse, scratch, dq, dk, dv, seg_start, seg_end, key_qend, T, heads,
+                                   kv_heads, q_pitch, k_pitch, v_pitch, scale, causal, dropout_p, dropout_seed, head_offset,
+                                   stream);
+}
+extern "C" int sb_attention_bwd_f16(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                    const float* lse, float* scratch, void* dq, void* dk, void* dv, const int* seg_start,
+                                    const int* seg_end, const int* key_qend, int T, int heads, int kv_heads,
+                                    long long q_pitch, long long k_pitch, long long v_pitch, float scale, int causal,
+                                    float dropout_p, unsigned long long dropout_seed, int head_offset, cudaStream_t stream) {
+  return attention_bwd_impl<true>(dout, q, k, v, out, lse, scratch, dq, dk, dv, seg_start, seg_end, key_qend, T, heads,
+                                  kv_heads, q_pitch, k_pitch, v_pitch, scale, causal, dropout_p, dropout_seed, head_offset,
+                                  stream);
 }

@@ -223,6 +223,12 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n, u
          | ((m >> 4) << 24);    // M / 16
 }
 
+// Same with fp16 operands (format code 0) when `half` is set: everything else about kind::f16 is shared.
+__host__ __device__ constexpr uint32_t make_idesc_16(uint32_t m, uint32_t n, uint32_t a_mn_major, uint32_t b_mn_major,
+                                                     bool half) {
+  return make_idesc_bf16(m, n, a_mn_major, b_mn_major) & ~(half ? ((1u << 7) | (1u << 10)) : 0u);
+}
+
 // ---------------------------------------------------------------------------------------------
 // cross-GPU flags (system scope) — used by the communication-fused kernels
 // ---------------------------------------------------------------------------------------------
@@ -254,6 +260,32 @@ SB_DEVICE uint32_t pack_bf16(float a, float b) {
 SB_DEVICE float2 unpack_bf16(uint32_t u) {
   __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
   return __bfloat1622float2(v);
+}
+// 16-bit storage format chosen at compile time: bf16 (default) or fp16.
+template <bool kHalf>
+SB_DEVICE uint32_t pack16(float a, float b) {
+  if constexpr (kHalf) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  } else {
+    return pack_bf16(a, b);
+  }
+}
+template <bool kHalf>
+SB_DEVICE float2 unpack16(uint32_t u) {
+  if constexpr (kHalf) {
+    return __half22float2(*reinterpret_cast<__half2*>(&u));
+  } else {
+    return unpack_bf16(u);
+  }
+}
+template <bool kHalf>
+SB_DEVICE float load16(const void* base, size_t i) {
+  if constexpr (kHalf) {
+    return __half2float(static_cast<const __half*>(base)[i]);
+  } else {
+    return __bfloat162float(static_cast<const __nv_bfloat16*>(base)[i]);
+  }
 }
 SB_DEVICE float warp_sum(float v) {
 #pragma unroll

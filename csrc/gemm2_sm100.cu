@@ -373,7 +373,8 @@ SB_DEVICE void split_reduce_chunk(uint32_t* v, const Params& p, const Sched& sc,
   for (int i = 0; i < kN; ++i) v[i] = __float_as_uint(acc[i]);
 }
 
-template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT>
+// kHalf: the 16-bit operands (and a 16-bit OutT) are fp16 instead of bf16 — plain store / accumulate epilogues only.
+template <int kAMajorMN, int kBMajorMN, int kEpi, typename OutT, bool kHalf = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kEpi == kAllReduce ? kArThreads : kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
              const __grid_constant__ CUtensorMap tma_a2, const __grid_constant__ CUtensorMap tma_b2, const Params p) {
@@ -478,7 +479,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, kAMajorMN, kBMajorMN);
+      static_assert(!kHalf || kEpi == kStore || kEpi == kAccumulate, "fp16 exists for the plain epilogues");
+      constexpr uint32_t idesc = make_idesc_16(BM, BN, kAMajorMN, kBMajorMN, kHalf);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -943,7 +945,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       } else {
         const int n0 = tn * BN;
         OutT* drow = reinterpret_cast<OutT*>(p.D) + (size_t)row * p.ldd;
-        const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+        const void* bias = p.bias;
 #pragma unroll 1
         for (int c = 0; c < BN; c += 32) {
           uint32_t v[32];
@@ -955,7 +957,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           if (col + 32 <= p.N) {
             if (bias) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __bfloat162float(bias[col + i]));
+              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + load16<kHalf>(bias, col + i));
             }
             if (sizeof(OutT) == 4) {
               float4* dst = reinterpret_cast<float4*>(drow + col);
@@ -978,18 +980,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
                 for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[8 * i + j]);
                 if (kEpi == kAccumulate) {
                   uint4 o = dst[i];
-                  float2 a = unpack_bf16(o.x), b = unpack_bf16(o.y), c2 = unpack_bf16(o.z), d = unpack_bf16(o.w);
+                  float2 a = unpack16<kHalf>(o.x), b = unpack16<kHalf>(o.y), c2 = unpack16<kHalf>(o.z),
+                         d = unpack16<kHalf>(o.w);
                   f[0] += a.x, f[1] += a.y, f[2] += b.x, f[3] += b.y, f[4] += c2.x, f[5] += c2.y, f[6] += d.x,
                       f[7] += d.y;
                 }
-                dst[i] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
-                                    pack_bf16(f[6], f[7]));
+                dst[i] = make_uint4(pack16<kHalf>(f[0], f[1]), pack16<kHalf>(f[2], f[3]), pack16<kHalf>(f[4], f[5]),
+                                    pack16<kHalf>(f[6], f[7]));
               }
             }
           } else {
             for (int i = 0; i < 32 && col + i < p.N; ++i) {
               float x = __uint_as_float(v[i]);
-              if (bias) x += __bfloat162float(bias[col + i]);
+              if (bias) x += load16<kHalf>(bias, col + i);
               if (kEpi == kAccumulate) x += (float)drow[col + i];
               drow[col + i] = (OutT)x;
             }
@@ -1134,9 +1137,9 @@ struct PendingGate {
 };
 static PendingGate g_pending_gate[64];
 
-template <int AM, int BMj, int EPI, typename OutT>
+template <int AM, int BMj, int EPI, typename OutT, bool kHalf = false>
 static int launch(const Maps& m, Params& p, cudaStream_t stream, int max_ctas) {
-  auto kern = gemm2_kernel<AM, BMj, EPI, OutT>;
+  auto kern = gemm2_kernel<AM, BMj, EPI, OutT, kHalf>;
   {
     int dev = 0;
     cudaGetDevice(&dev);
@@ -1263,6 +1266,33 @@ extern "C" int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* 
                              cudaStream_t stream) {
   return gemm2_impl(A, B, D, bias, M, N, K, lda, ldb, ldd, a_layout, b_layout, out_dtype, epilogue, nullptr, max_ctas,
                     stream);
+}
+
+// fp16 operands on the same kernel (reference acceptance grid: fp16 + dynamic loss scaler,
+// tests/core/test_training/test_training.py:149-235): fprop (a_layout 0, b_layout 0), dgrad (0, 1) and wgrad (1, 1) of a
+// linear layer.  out_dtype 0 = fp16, 1 = fp32; epilogue 1 accumulates into D (fp32 main-grad arenas); bias is fp16.
+// The tensor maps are shared with the bf16 path: their element type only sizes the 2-byte elements.
+extern "C" int sb_gemm2_f16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb,
+                            int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas,
+                            cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  Params p{};
+  Maps m;
+  if (int rc = make_maps(m, A, B, M, N, K, lda, ldb, a_layout, b_layout, nullptr, p)) return rc;
+  p.M = M, p.N = N, p.K = K, p.D = D, p.ldd = ldd, p.bias = bias;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + BN - 1) / BN;
+  if (a_layout == 0 && b_layout == 0 && epilogue == 0 && out_dtype == 0)
+    return launch<0, 0, kStore, __half, true>(m, p, stream, max_ctas);
+  if (a_layout == 0 && b_layout == 1 && epilogue == 0 && out_dtype == 0)
+    return launch<0, 1, kStore, __half, true>(m, p, stream, max_ctas);
+  if (a_layout == 1 && b_layout == 1 && epilogue == 0 && out_dtype == 0)
+    return launch<1, 1, kStore, __half, true>(m, p, stream, max_ctas);
+  if (a_layout == 1 && b_layout == 1 && epilogue == 0 && out_dtype == 1)
+    return launch<1, 1, kStore, float, true>(m, p, stream, max_ctas);
+  if (a_layout == 1 && b_layout == 1 && epilogue == 1 && out_dtype == 1)
+    return launch<1, 1, kAccumulate, float, true>(m, p, stream, max_ctas);
+  return -10;
 }
 
 // LoRA-fused linear: D[M,N] (+)= A·Bᵀ + A2·B2ᵀ in ONE accumulator — the low-rank pair rides as extra

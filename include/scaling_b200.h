@@ -33,6 +33,12 @@ int sb_gemm2_bf16(const void* A, const void* B, void* D, const void* bias, int M
                   int ldd, int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas, cudaStream_t st);
 int sb_gemm2_swiglu_bf16(const void* X, const void* W, void* H, void* pre, int M, int F, int K, int ldx, int ldw,
                          int ldh, int ldpre, int max_ctas, cudaStream_t st);
+/* fp16 operands on the same 2-CTA kernel, for the three GEMMs of a linear layer: fprop (a_layout 0, b_layout 0), dgrad
+ * (0, 1), wgrad (1, 1).  out_dtype 0 = fp16, 1 = fp32 (wgrad only); epilogue 1 accumulates into an fp32 D (wgrad only);
+ * bias is fp16.  Returns -10 for any other combination.  Reference counterpart: the fp16 + dynamic-loss-scaler
+ * training grid (tests/core/test_training/test_training.py:149-235), cuBLAS behind F.linear. */
+int sb_gemm2_f16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K, int lda, int ldb, int ldd,
+                 int a_layout, int b_layout, int out_dtype, int epilogue, int max_ctas, cudaStream_t st);
 /* Split-K tail workspace of the 2-CTA GEMMs: size for the current device, and registration (once per device, with that
  * device current) of a caller-owned 16-byte aligned buffer of at least that size whose trailing counter words are
  * zero.  GEMMs that split must then be issued on one stream at a time per device.  NULL unregisters. */
@@ -160,6 +166,18 @@ int sb_attention_bwd_ex(const void* dout, const void* q, const void* k, const vo
                         const int* key_qend, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
                         long long v_pitch, float scale, int causal, float dropout_p, unsigned long long dropout_seed,
                         int head_offset, cudaStream_t st);
+
+/* sb_attention_fwd_ex / sb_attention_bwd_ex with fp16 tensors (q, k, v, out, dout, dq, dk, dv and the probabilities
+ * handed back to the tensor core are fp16; statistics stay fp32). */
+int sb_attention_fwd_f16(const void* q, const void* k, const void* v, void* out, float* lse, const int* seg_start,
+                         const int* seg_end, int T, int Tk, int heads, int kv_heads, long long q_pitch, long long k_pitch,
+                         long long v_pitch, float scale, int causal, float dropout_p, unsigned long long dropout_seed,
+                         int head_offset, cudaStream_t st);
+int sb_attention_bwd_f16(const void* dout, const void* q, const void* k, const void* v, const void* out, const float* lse,
+                         float* scratch, void* dq, void* dk, void* dv, const int* seg_start, const int* seg_end,
+                         const int* key_qend, int T, int heads, int kv_heads, long long q_pitch, long long k_pitch,
+                         long long v_pitch, float scale, int causal, float dropout_p, unsigned long long dropout_seed,
+                         int head_offset, cudaStream_t st);
 
 /* Bind `device`'s primary context to the calling thread (tensor-map encoding is a driver call and needs one; PyTorch's
  * autograd worker threads set their device lazily). */

@@ -25,6 +25,7 @@ _SIGS = {
     "sb_gemm_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm_swiglu_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_bf16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
+    "sb_gemm2_f16": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P],
     "sb_gemm2_lowrank_bf16": [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                               c_int, c_int, P],
     "sb_gemm2_allreduce_lowrank_bf16": [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
@@ -63,6 +64,10 @@ _SIGS = {
                             c_int, c_float, c_ulonglong, c_int, P],
     "sb_attention_bwd_ex": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
                             c_float, c_int, c_float, c_ulonglong, c_int, P],
+    "sb_attention_fwd_f16": [P, P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong, c_float,
+                             c_int, c_float, c_ulonglong, c_int, P],
+    "sb_attention_bwd_f16": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
+                             c_float, c_int, c_float, c_ulonglong, c_int, P],
     "sb_attention_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_longlong,
                          c_float, c_int, P],
     "sb_grad_sumsq": [P, c_longlong, c_int, P, P, c_int, P, P],

@@ -125,7 +125,7 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: t
         if fusable:
             from .attention_sm100 import sm100_attention_supported
 
-            # no library kernel behind "auto": what the sm_100a kernel does not cover (fp16, head dims above 128,
+            # no library kernel behind "auto": what the sm_100a kernel does not cover (head dims above 128,
             # gradients through a KV cache) runs the plain PyTorch expression; the flash-attn
             # wheel is only used when asked for by name (SCALING_B200_ATTENTION=flash, A/B measurements)
             if sm100_attention_supported(q, k, v, cu_seqlens_q, cu_k, causal, window, p):

@@ -13,14 +13,14 @@ _BWD_IMPL = os.environ.get("SCALING_B200_ATTENTION_BWD", "auto")  # auto | sm100
 
 
 def sm100_attention_supported(q, k, v, cu_q, cu_k, causal, window, dropout_p) -> bool:
-    """bf16, head dim <= 128 (smaller heads are zero-padded to the kernel's 128), GQA/MQA, packed sequences, causal or
+    """bf16 or fp16, head dim <= 128 (smaller heads are zero-padded to the kernel's 128), GQA/MQA, packed sequences, causal or
     bidirectional, sliding windows, attention-probability dropout (stateless hash mask); keys may differ from queries
     (KV-cache decoding) when no gradient is needed."""
     lib = _lib.load() if torch.cuda.is_available() else None
     if lib is None or not hasattr(lib, "sb_attention_fwd_ex"):
         return False
     d = q.shape[-1]
-    if not (q.dtype == torch.bfloat16 and d <= 128 and d % 8 == 0 and 0.0 <= dropout_p < 1.0 and q.shape[1] % k.shape[1] == 0):
+    if not (q.dtype in (torch.bfloat16, torch.float16) and k.dtype == q.dtype and v.dtype == q.dtype and d <= 128 and d % 8 == 0 and 0.0 <= dropout_p < 1.0 and q.shape[1] % k.shape[1] == 0):
         return False
     if cu_q is not cu_k and (q.requires_grad or k.requires_grad or v.requires_grad) and torch.is_grad_enabled():
         return False  # decoding against a cache is forward only
@@ -85,7 +85,7 @@ def attention_fwd(q, k, v, seg_start, seg_end, causal: bool, scale: float, dropo
     T, heads, d = q.shape
     out = torch.empty((T, heads, d), dtype=q.dtype, device=q.device)
     lse = torch.empty((heads, T), dtype=torch.float32, device=q.device)
-    call("sb_attention_fwd_ex", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, k.shape[0],
+    call("sb_attention_fwd_f16" if q.dtype == torch.float16 else "sb_attention_fwd_ex", ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(seg_start), ptr(seg_end), T, k.shape[0],
          heads, k.shape[1], q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal), float(dropout[0]),
          int(dropout[1]) & 0xFFFFFFFFFFFFFFFF, int(dropout[2]))
     return out, lse
@@ -121,7 +121,7 @@ def attention_bwd(dout, q, k, v, out, lse, seg_start, seg_end, causal: bool, sca
     dk = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     dv = torch.empty((T, kvh, d), dtype=q.dtype, device=q.device)
     delta = _bwd_scratch(q.device, T, heads)
-    call("sb_attention_bwd_ex", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
+    call("sb_attention_bwd_f16" if q.dtype == torch.float16 else "sb_attention_bwd_ex", ptr(dout), ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
          ptr(seg_start), ptr(seg_end), ptr(key_qend), T, heads, kvh, q.stride(0), k.stride(0), v.stride(0), float(scale), int(causal),
          float(dropout[0]), int(dropout[1]) & 0xFFFFFFFFFFFFFFFF, int(dropout[2]), launches=3)
     return dq, dk, dv

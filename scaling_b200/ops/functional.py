@@ -43,14 +43,19 @@ def _aligned(*dims: int) -> bool:
     return all(d % 8 == 0 and d > 0 for d in dims)
 
 
+def _own_gemm(t: torch.Tensor, m: int, n: int) -> bool:
+    """bf16 runs every shape on the own kernels; fp16 exists on the 2-CTA kernel (tiles of 256 x 256) only."""
+    return _PLAIN_GEMM != "cublas" and (t.dtype == torch.bfloat16 or (m >= 256 and n >= 128))
+
+
 def _gemm_nt(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    if _PLAIN_GEMM == "cublas":
+    if not _own_gemm(x, x.shape[0], w.shape[0]):
         return F.linear(x, w, bias)
     return K.gemm(x, w, bias=bias)
 
 
 def _gemm_nn(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    if _PLAIN_GEMM == "cublas":
+    if not _own_gemm(dy, dy.shape[0], w.shape[1]):
         return dy @ w
     return K.gemm(dy, w, b_mn=True)
 
@@ -62,7 +67,7 @@ def _fusable(m: int, n: int) -> bool:
 
 def _gemm_nt_reduce(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], comm) -> torch.Tensor:
     """Σ_tp x_r·w_rᵀ (+ bias once): one fused launch, or GEMM + NCCL all-reduce for shapes below the 2-CTA tile."""
-    if _fusable(x.shape[0], w.shape[0]):
+    if _fusable(x.shape[0], w.shape[0]) and x.dtype == torch.bfloat16:
         return K.gemm_allreduce(x, w, comm, bias=bias)
     y = _gemm_nt(x, w)
     comm.all_reduce_(y)
@@ -70,7 +75,7 @@ def _gemm_nt_reduce(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tenso
 
 
 def _gemm_nn_reduce(dy: torch.Tensor, w: torch.Tensor, comm) -> torch.Tensor:
-    if _fusable(dy.shape[0], w.shape[1]):
+    if _fusable(dy.shape[0], w.shape[1]) and dy.dtype == torch.bfloat16:
         return K.gemm_allreduce(dy, w, comm, b_mn=True)
     return comm.all_reduce_(_gemm_nn(dy, w))
 
@@ -99,10 +104,14 @@ class _ReduceFromRegion(torch.autograd.Function):
 def _accumulate_wgrad(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> Optional[torch.Tensor]:
     """dW = dyᵀ·x. Into ``weight.main_grad`` (returns None) or as a fresh tensor."""
     main = getattr(weight, "main_grad", None)
+    own = _own_gemm(dy, dy.shape[1], x.shape[1])
     if main is not None:
-        K.gemm(dy, x, a_mn=True, b_mn=True, out=main, accumulate=True)
+        if own or dy.dtype == torch.bfloat16:
+            K.gemm(dy, x, a_mn=True, b_mn=True, out=main, accumulate=True)
+        else:
+            main.add_((dy.t() @ x).to(main.dtype))
         return None
-    if _PLAIN_GEMM == "cublas":
+    if not own:
         return dy.t() @ x
     return K.gemm(dy, x, a_mn=True, b_mn=True, out_dtype=weight.dtype)
 
@@ -186,9 +195,9 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     With a :class:`~scaling_b200.parallel.TPComm`: ``reduce_output`` sums y over the TP group (row-parallel forward;
     the bias is added once, after the sum) and ``reduce_input_grad`` sums dX over it (column-parallel backward) —
     each inside the GEMM launch that produces the operand, instead of an NCCL all-reduce behind it."""
-    if (native_enabled(x) and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    if (native_enabled(x) and x.dtype in (torch.bfloat16, torch.float16) and weight.dtype == x.dtype
             and _aligned(weight.shape[0], weight.shape[1]) and x.numel() > 0
-            and (bias is None or bias.dtype == torch.bfloat16)):
+            and (bias is None or bias.dtype == x.dtype)):
         return _LinearFn.apply(x, weight, bias, comm, reduce_output, reduce_input_grad)
     if comm is None:
         return F.linear(x, weight, bias)

@@ -69,6 +69,17 @@ def gemm_supported(M: int, N: int, K: int, lda: int, ldb: int, ldd: int) -> bool
     return M > 0 and N > 0 and K > 0 and lda % 8 == 0 and ldb % 8 == 0 and ldd % 8 == 0
 
 
+def gemm_f16_supported(M: int, N: int, a_mn: bool, b_mn: bool, out_dtype: torch.dtype = torch.float16,
+                       accumulate: bool = False) -> bool:
+    """fp16 operands: fprop (row-major x row-major), dgrad (b_mn) and wgrad (a_mn and b_mn) of a linear layer on the
+    2-CTA kernel (M >= 256, N >= 128); fp32 output / accumulation for the wgrad only (main-grad arenas)."""
+    if M < 256 or N < 128 or (a_mn and not b_mn):
+        return False
+    if out_dtype == torch.float32:
+        return a_mn and b_mn
+    return not accumulate
+
+
 def gemm(
     a: torch.Tensor,
     b: torch.Tensor,
@@ -76,7 +87,7 @@ def gemm(
     a_mn: bool = False,
     b_mn: bool = False,
     out: Optional[torch.Tensor] = None,
-    out_dtype: torch.dtype = torch.bfloat16,
+    out_dtype: Optional[torch.dtype] = None,
     accumulate: bool = False,
     bias: Optional[torch.Tensor] = None,
     max_ctas: int = 0,
@@ -84,9 +95,14 @@ def gemm(
     """D[M,N] (+)= A · Bᵀ on the tcgen05 kernel.
 
     a: [M,K] row-major, or [K,M] when ``a_mn``;  b: [N,K] row-major, or [K,N] when ``b_mn``.  Rows may be strided
-    (``stride(0)`` is the leading dimension) but the inner dimension must be contiguous.
+    (``stride(0)`` is the leading dimension) but the inner dimension must be contiguous.  bf16 operands take every
+    layout; fp16 operands the three layouts of a linear layer (see :func:`gemm_f16_supported`).  The result is in the
+    operands' dtype unless ``out`` / ``out_dtype`` say fp32.
     """
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+    assert a.dtype == b.dtype and a.dtype in (torch.bfloat16, torch.float16) and a.dim() == 2 and b.dim() == 2
+    half = a.dtype == torch.float16
+    if out_dtype is None:
+        out_dtype = a.dtype
     assert a.stride(1) == 1 and b.stride(1) == 1
     if a_mn:
         K, M = a.shape
@@ -100,19 +116,25 @@ def gemm(
     if out is None:
         assert not accumulate
         out = torch.empty((M, N), dtype=out_dtype, device=a.device)
-    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
+    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype in (a.dtype, torch.float32)
     assert a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0 and out.data_ptr() % 16 == 0
     lda, ldb, ldd = a.stride(0), b.stride(0), out.stride(0)
     assert gemm_supported(M, N, K, lda, ldb, ldd), "leading dimensions must be multiples of 8 elements"
     if bias is not None:
-        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+        assert bias.dtype == a.dtype and bias.numel() == N and bias.is_contiguous()
     try:
-        entry = _gemm_entry(M, N, a.device)
+        if half:
+            assert gemm_f16_supported(M, N, a_mn, b_mn, out.dtype, accumulate), \
+                "fp16 runs the linear-layer layouts of the 2-CTA kernel only"
+            _ensure_split_workspace(a.device)
+            entry = "sb_gemm2_f16"
+        else:
+            entry = _gemm_entry(M, N, a.device)
         if not a_mn:
             _apply_gate(a, entry)
         call(
             entry, ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
-            DTYPE_CODE[out.dtype], int(accumulate), max_ctas,
+            int(out.dtype == torch.float32), int(accumulate), max_ctas,
         )
     except RuntimeError as e:
         raise RuntimeError(
