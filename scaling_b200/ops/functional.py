@@ -9,6 +9,7 @@ weight gradient — no per-micro-batch ``.grad`` tensors, no separate accumulati
 from __future__ import annotations
 
 import os
+import weakref
 from typing import Any, Optional, Tuple
 
 import torch
@@ -214,9 +215,9 @@ def _gather_dim(t: torch.Tensor, dim: int, tp) -> torch.Tensor:
     size, _, group = tp
     if size == 1:
         return t
-    parts = torch.empty((size, *t.shape), dtype=t.dtype, device=t.device)
-    torch.distributed.all_gather_into_tensor(parts, t.contiguous(), group=group)
-    return torch.cat(list(parts.unbind(0)), dim=dim).contiguous()
+    flat = torch.empty(size * t.numel(), dtype=t.dtype, device=t.device)  # flat: the layout every backend accepts
+    torch.distributed.all_gather_into_tensor(flat, t.contiguous().view(-1), group=group)
+    return torch.cat(list(flat.view(size, *t.shape).unbind(0)), dim=dim).contiguous()
 
 
 _WEIGHT_EPOCH = 0
@@ -239,12 +240,13 @@ def _row_lora_operands(A: torch.Tensor, B: torch.Tensor, tp, kl: int) -> Tuple[t
     key = (A.data_ptr(), B.data_ptr(), kl)
     stamp = (_WEIGHT_EPOCH, A._version, B._version)
     hit = _ROW_LORA_CACHE.get(key)
-    if hit is not None and hit[0] == stamp:
+    # the entry belongs to these very tensor objects: another model allocated at the same addresses must not hit it
+    if hit is not None and hit[0] == stamp and hit[3]() is A and hit[4]() is B:
         return hit[1], hit[2]
     with torch.no_grad():
         a_cols = _gather_dim(A, 0, tp)[:, rank * kl:(rank + 1) * kl].contiguous()
         b_full = _gather_dim(B, 1, tp)
-    _ROW_LORA_CACHE[key] = (stamp, a_cols, b_full)
+    _ROW_LORA_CACHE[key] = (stamp, a_cols, b_full, weakref.ref(A), weakref.ref(B))
     return a_cols, b_full
 
 

@@ -274,3 +274,41 @@ def test_tensor_parallel_parity_gloo():
         assert o["linear_fwd"] < 1e-5 and o["linear_dx"] < 1e-4 and o["linear_dwc"] < 1e-4 and o["linear_dwr"] < 1e-4, o
         assert o["emb_fwd"] == 0.0
     assert res[0]["emb_trainable_rows"] == [1] and res[1]["emb_trainable_rows"] == [7]
+
+
+# --------------------------------------------------------------------------------------------------- row-LoRA operands
+def _row_lora_cache_worker(rank: int, world_size: int, master_port: int):
+    import torch.distributed as dist
+
+    from scaling_b200.ops import functional as OF
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{master_port}", rank=rank, world_size=world_size)
+    try:
+        torch.manual_seed(0)
+        r, kl, n = 8, 6, 10
+        a_full, b_full = torch.randn(r, kl * world_size), torch.randn(n, r)
+        rl = r // world_size
+        A = a_full[rank * rl:(rank + 1) * rl].clone()  # rank dimension is TP-split, all input columns
+        B = b_full[:, rank * rl:(rank + 1) * rl].clone()
+        tp = (world_size, rank, dist.group.WORLD)
+        a1, b1 = OF._row_lora_operands(A, B, tp, kl)
+        assert torch.equal(a1, a_full[:, rank * kl:(rank + 1) * kl]) and torch.equal(b1, b_full)
+        a2, _ = OF._row_lora_operands(A, B, tp, kl)
+        assert a2 is a1, "same weights within a step: the gathers run once"
+        A.mul_(2.0)  # in-place change seen by autograd's version counter
+        a3, _ = OF._row_lora_operands(A, B, tp, kl)
+        assert a3 is not a1 and torch.equal(a3, 2.0 * a_full[:, rank * kl:(rank + 1) * kl])
+        OF.bump_weight_epoch()  # what the optimizer's arena kernels announce
+        a4, _ = OF._row_lora_operands(A, B, tp, kl)
+        assert a4 is not a3
+        # another tensor object at the same address must not hit the entry
+        alias = A.view_as(A)
+        a5, _ = OF._row_lora_operands(alias, B, tp, kl)
+        assert a5 is not a4
+        return True
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_lora_operands_are_gathered_once_per_weight_version():
+    assert all(dist_launcher(_row_lora_cache_worker, world_size=2).values())

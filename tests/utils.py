@@ -10,10 +10,7 @@ import torch
 import torch.multiprocessing as mp
 
 
-def find_free_port() -> int:
-    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
-        s.bind(("127.0.0.1", 0))
-        return int(s.getsockname()[1])
+from scaling_b200.core.utils.port import find_free_port  # noqa: E402,F401  (ports below the ephemeral range)
 
 
 def _worker(rank: int, world: int, port: int, fn: Callable, kwargs: Dict[str, Any], results: Any) -> None:
