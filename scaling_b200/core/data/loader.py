@@ -68,8 +68,19 @@ class DataLoader:
             dataset, batch_size=topology.config.micro_batch_size, sampler=self.sampler, num_workers=num_workers,
             pin_memory=pin_memory and torch.cuda.is_available(), collate_fn=dataset.collate, drop_last=True, **kwargs,
         )
+        self._it = self._fresh_iterator()
+
+    def _fresh_iterator(self) -> Iterator[Any]:
+        """New torch iterator for the sampler's current epoch.  Torch draws the workers' base seed from the default CPU
+        generator when an iterator is made; a resumed run makes its iterator at a different point of the random stream
+        than the run it continues (after the checkpoint's RNG state is restored, or not at an epoch boundary), so the
+        draw is taken back: everything that samples from the default generator afterwards (CPU dropout) stays
+        bit-identical across a resume."""
         self.sampler.seed_current_epoch()
-        self._it = iter(self.loader)
+        state = torch.get_rng_state()
+        it = iter(self.loader)
+        torch.set_rng_state(state)
+        return it
 
     def __iter__(self) -> "DataLoader":
         return self
@@ -79,6 +90,5 @@ class DataLoader:
             return next(self._it)
         except StopIteration:
             # epoch boundary: a fresh torch iterator forks fresh workers AFTER the sampler re-seeded the dataset
-            self.sampler.seed_current_epoch()
-            self._it = iter(self.loader)
+            self._it = self._fresh_iterator()
             return next(self._it)

@@ -35,10 +35,14 @@ def test_sequence_parallel_matches_tensor_parallel(tmp_path, data):
 def test_transformer_resume_exact(tmp_path, data, mp, pp):
     ckpt = tmp_path / "ckpt"
     world = mp * pp
+    # every kind of dropout: the counter-based ones (embedding, after attention / MLP) and the attention-probability
+    # dropout of the dense path, which samples torch's default generator (reference acceptance test:
+    # tests/transformer/test_training.py:150-300 resumes at 1e-10 with all four at 0.1)
+    drop = {"dropout_after_mlp": 0.1, "dropout_after_attention": 0.1, "dropout_embedding": 0.1, "dropout_attention_probs": 0.1}
     full = dist_launcher(run_transformer, world, config_dict=tiny_config(
-        data, mp, pp, 1, iters=8, trainer={"save_dir": str(ckpt), "save_interval": 5}, arch={"dropout_after_mlp": 0.1}))[0]
+        data, mp, pp, 1, iters=8, trainer={"save_dir": str(ckpt), "save_interval": 5}, arch=drop))[0]
     resumed = dist_launcher(run_transformer, world, config_dict=tiny_config(
-        data, mp, pp, 1, iters=8, trainer={"load_dir": str(ckpt)}, arch={"dropout_after_mlp": 0.1}))[0]
+        data, mp, pp, 1, iters=8, trainer={"load_dir": str(ckpt)}, arch=drop))[0]
     assert resumed == full[5:], (full, resumed)
 
 

@@ -4,7 +4,9 @@ The reference's tests are staged in a scratch directory (nothing of them is copi
 root goes on PYTHONPATH so that ``import scaling`` resolves to the alias (scaling/__init__.py) and ``import
 blended_dataset_loop`` to the C++-backed shim, and pytest's summary is written to ``profiles/reference_cpu_tests_r2.json``.
 
-    python tools/run_reference_tests.py [--reference /root/reference]
+    python tools/run_reference_tests.py [--reference /root/reference]            # CPU unit files
+    python tools/run_reference_tests.py --suite gpu                              # acceptance suites, on a GPU box
+    python tools/run_reference_tests.py --suite gpu --fake-devices 1             # same on CPU / gloo (dry run)
 """
 import argparse
 import json
@@ -26,23 +28,86 @@ TARGETS = [
     "tests/transformer/test_utils.py",
 ]
 
+# the reference's accelerator test files (SURVEY §4.1 training / transformer suites): they skip a case when it needs more
+# devices than the box has, so one GPU runs every world-size-1 case and N GPUs the rest
+GPU_TARGETS = [
+    "tests/transformer/test_training.py", "tests/transformer/test_training_flash_attention.py",
+    "tests/transformer/test_training_local_attention.py", "tests/transformer/test_training_sequence_parallel.py",
+    "tests/transformer/test_training_legacy.py", "tests/transformer/test_training_finetuning_chat.py",
+    "tests/transformer/test_finetuning.py", "tests/transformer/test_inference.py",
+    "tests/transformer/test_load_checkpoint_non_strict.py", "tests/transformer/test_backwards_compatibility.py",
+    "tests/transformer/test_data.py", "tests/transformer/test_blended_dataset.py",
+    "tests/core/test_training", "tests/core/test_nn", "tests/core/test_optimizer",
+]
+DETERMINED_STUB = '''"""Scratch stand-in so that test modules which import the Determined SDK at module level can be collected without
+it; cases that really use Determined are deselected."""
+import types
+
+
+class _Obj:
+    def __init__(self, *a, **k):
+        self.__dict__.update(k)
+
+
+ClusterInfo = TrialInfo = RendezvousInfo = _Obj
+
+
+def get_cluster_info():
+    return None
+
+
+core = types.SimpleNamespace(Context=_Obj, DistributedContext=_Obj, DummyDistributedContext=_Obj, TrainContext=_Obj,
+                             CheckpointContext=_Obj, init=lambda *a, **k: None)
+'''
+SKIP_EXPR = "world_size > torch.cuda.device_count()"
+
 p = argparse.ArgumentParser()
 p.add_argument("--reference", default="/root/reference")
-p.add_argument("--out", default=str(REPO / "profiles" / "reference_cpu_tests_r2.json"))
+p.add_argument("--suite", choices=["cpu", "gpu"], default="cpu",
+               help="cpu: the CPU-capable unit files; gpu: the training / transformer acceptance suites")
+p.add_argument("--fake-devices", type=int, default=0,
+               help="gpu suite on a box without GPUs (gloo dry run): pretend this many devices in the tests' skip check")
+p.add_argument("--select", default=None, help="pytest -k expression")
+p.add_argument("--targets", nargs="*", default=None, help="override the file list of the suite")
+p.add_argument("--timeout", type=int, default=900, help="per-test timeout (pytest-timeout)")
+p.add_argument("--out", default=None)
 a = p.parse_args()
+targets = a.targets or (TARGETS if a.suite == "cpu" else GPU_TARGETS)
+out = a.out or str(REPO / "profiles" / f"reference_{a.suite}_tests_r2.json")
 
 with tempfile.TemporaryDirectory(prefix="reftests_") as tmp:
     shutil.copytree(Path(a.reference) / "tests", Path(tmp) / "tests")
+    try:
+        import determined  # noqa: F401
+        have_determined = True
+    except ImportError:
+        have_determined = False
+        (Path(tmp) / "determined.py").write_text(DETERMINED_STUB)
+    if a.fake_devices:
+        for f in (Path(tmp) / "tests").rglob("*.py"):
+            src = f.read_text()
+            if SKIP_EXPR in src:
+                f.write_text(src.replace(SKIP_EXPR, f"world_size > max(torch.cuda.device_count(), {a.fake_devices})"))
+    select = a.select
+    if a.suite == "gpu" and not have_determined:
+        select = f"({select}) and not determined" if select else "not determined"
     env = dict(os.environ, PYTHONPATH=str(REPO))
-    r = subprocess.run([sys.executable, "-m", "pytest", *TARGETS, "-q", "-p", "no:cacheprovider",
-                        "--continue-on-collection-errors", "-rfE"], cwd=tmp, env=env, capture_output=True, text=True)
+    cmd = [sys.executable, "-m", "pytest", *targets, "-q", "-p", "no:cacheprovider", "--continue-on-collection-errors",
+           "-rfE", "--timeout", str(a.timeout)]
+    if select:
+        cmd += ["-k", select]
+    r = subprocess.run(cmd, cwd=tmp, env=env, capture_output=True, text=True)
 tail = r.stdout.strip().splitlines()
 summary = tail[-1] if tail else ""
-counts = {k: int(v) for v, k in re.findall(r"(\d+) (passed|failed|skipped|errors?|warnings?)", summary)}
+counts = {k: int(v) for v, k in re.findall(r"(\d+) (passed|failed|skipped|deselected|errors?|warnings?)", summary)}
 not_passing = sorted({ln.split(" - ")[0] for ln in tail if ln.startswith(("FAILED ", "ERROR "))})
-json.dump({"targets": TARGETS, "summary": summary, "counts": counts, "not_passing": not_passing,
+json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices,
+           "cuda_devices": __import__("torch").cuda.device_count(), "summary": summary, "counts": counts,
+           "not_passing": not_passing,
            "note": "collection errors are test files that import private helpers of the reference's implementation "
-                   "(names starting with an underscore) which are not part of its API"}, open(a.out, "w"), indent=1)
+                   "(names starting with an underscore) which are not part of its API"}, open(out, "w"), indent=1)
 print(summary)
 for ln in not_passing:
     print(" ", ln)
+if os.environ.get("REFTESTS_VERBOSE"):
+    print("\n".join(tail[-200:]))
