@@ -306,6 +306,39 @@ __global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const __
   }
 }
 
+// Deterministic variant: `ids` are sorted (stable, so equal ids keep their token order) and `perm[i]` is the token the
+// i-th sorted id came from.  The block that sits on the first position of a run of equal ids sums the run's rows in that
+// fixed order and adds the total to the row of dW — no atomics, the same bits on every run (the reference's path,
+// ATen's sort + segmented embedding backward, is deterministic as well, and its resume test compares losses to 1e-10).
+template <typename G>
+__global__ void embedding_bwd_sorted_kernel(const long long* __restrict__ ids, const long long* __restrict__ perm,
+                                            const __nv_bfloat16* __restrict__ dout, G* __restrict__ dW, int tokens,
+                                            int hidden, long long vocab_start, long long vocab_end) {
+  for (int i = blockIdx.x; i < tokens; i += gridDim.x) {
+    const long long id = ids[i];
+    if (i > 0 && ids[i - 1] == id) continue;  // not the head of its run
+    if (id < vocab_start || id >= vocab_end) continue;
+    G* dst = dW + (size_t)(id - vocab_start) * hidden;
+    for (int c = threadIdx.x * 2; c < hidden; c += blockDim.x * 2) {
+      float ax = 0.f, ay = 0.f;
+      for (int j = i; j < tokens && ids[j] == id; ++j) {
+        const float2 d = unpack_bf16(*reinterpret_cast<const uint32_t*>(dout + (size_t)perm[j] * hidden + c));
+        ax += d.x, ay += d.y;
+      }
+      if constexpr (sizeof(G) == 4) {
+        float2* o = reinterpret_cast<float2*>(dst + c);
+        float2 v = *o;
+        v.x += ax, v.y += ay;
+        *o = v;
+      } else {
+        uint32_t* o = reinterpret_cast<uint32_t*>(dst + c);
+        const float2 v = unpack_bf16(*o);
+        *o = pack_bf16(v.x + ax, v.y + ay);
+      }
+    }
+  }
+}
+
 static int blocks_for(size_t work, int threads = 256) {
   size_t b = (work + threads - 1) / threads;
   size_t cap = 148 * 16;
@@ -561,5 +594,19 @@ extern "C" int sb_embedding_bwd(const long long* ids, const void* dout, void* dW
     embedding_bwd_kernel<float><<<b, 256, 0, st>>>(ids, (const __nv_bfloat16*)dout, (float*)dW, tokens, hidden, vocab_start, vocab_end);
   else
     embedding_bwd_kernel<__nv_bfloat16><<<b, 256, 0, st>>>(ids, (const __nv_bfloat16*)dout, (__nv_bfloat16*)dW, tokens, hidden, vocab_start, vocab_end);
+  return (int)cudaGetLastError();
+}
+extern "C" int sb_embedding_bwd_sorted(const long long* sorted_ids, const long long* perm, const void* dout, void* dW,
+                                       int grad_fp32, int tokens, int hidden, long long vocab_start, long long vocab_end,
+                                       cudaStream_t st) {
+  if (tokens <= 0) return 0;
+  if (hidden % 2) return -1;
+  const int b = tokens < 148 * 16 ? tokens : 148 * 16;
+  if (grad_fp32)
+    embedding_bwd_sorted_kernel<float><<<b, 128, 0, st>>>(sorted_ids, perm, (const __nv_bfloat16*)dout, (float*)dW, tokens,
+                                                          hidden, vocab_start, vocab_end);
+  else
+    embedding_bwd_sorted_kernel<__nv_bfloat16><<<b, 128, 0, st>>>(sorted_ids, perm, (const __nv_bfloat16*)dout,
+                                                                  (__nv_bfloat16*)dW, tokens, hidden, vocab_start, vocab_end);
   return (int)cudaGetLastError();
 }

@@ -218,6 +218,10 @@ int sb_embedding_fwd(const long long* ids, const void* W, void* out, int tokens,
                      long long vocab_end, cudaStream_t st);
 int sb_embedding_bwd(const long long* ids, const void* dout, void* dW, int grad_fp32, int tokens, int hidden,
                      long long vocab_start, long long vocab_end, cudaStream_t st);
+/* Deterministic form: sorted_ids = stable sort of the token ids, perm = the token each sorted id came from; one block per
+ * run of equal ids sums the run in token order and adds it to dW without atomics. */
+int sb_embedding_bwd_sorted(const long long* sorted_ids, const long long* perm, const void* dout, void* dW, int grad_fp32,
+                            int tokens, int hidden, long long vocab_start, long long vocab_end, cudaStream_t st);
 
 /* ---- vocab-parallel cross-entropy (csrc/xent.cu) — transformer/model/model.py:56-76,
  *      transformer/model/layers/lm_head_tied.py:41-43 ---- */

@@ -49,6 +49,7 @@ _SIGS = {
     "sb_dropout_bwd": [P, P, c_longlong, c_float, c_ulonglong, c_ulonglong, P],
     "sb_embedding_fwd": [P, P, P, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_bwd": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
+    "sb_embedding_bwd_sorted": [P, P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, P],
     "sb_embedding_fwd_peers": [P, P, P, c_int, c_int, c_int, c_longlong, c_longlong, c_int, P],
     "sb_seq_gather_push": [P, P, c_int, c_int, c_int, c_int, c_int, P],
     "sb_seq_gather_push_counted": [P, P, P, c_int, c_int, c_int, c_int, c_int, P],

@@ -435,11 +435,21 @@ def embedding_fwd(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, voc
     return out
 
 
+_EMBEDDING_BWD = os.environ.get("SCALING_B200_EMBEDDING_BWD", "sorted")
+
+
 def embedding_bwd(ids: torch.Tensor, dout: torch.Tensor, dweight: torch.Tensor, vocab_start: int, vocab_end: int) -> None:
-    """dweight (fp32 or bf16, [V_local, hidden]) += scatter(dout) — accumulates in place."""
+    """dweight (fp32 or bf16, [V_local, hidden]) += scatter(dout) — accumulates in place.  Deterministic: the ids are
+    sorted (stable) and every run of equal ids is summed in token order by one block; ``SCALING_B200_EMBEDDING_BWD=atomic``
+    selects the atomicAdd scatter (faster for tiny batches, summation order varies from run to run)."""
     assert dout.is_contiguous() and dweight.is_contiguous()
-    call("sb_embedding_bwd", ptr(ids), ptr(dout), ptr(dweight), int(dweight.dtype == torch.float32), ids.numel(),
-         dweight.shape[1], vocab_start, vocab_end)
+    if _EMBEDDING_BWD == "atomic":
+        call("sb_embedding_bwd", ptr(ids), ptr(dout), ptr(dweight), int(dweight.dtype == torch.float32), ids.numel(),
+             dweight.shape[1], vocab_start, vocab_end)
+        return
+    sorted_ids, perm = torch.sort(ids.reshape(-1).long(), stable=True)
+    call("sb_embedding_bwd_sorted", ptr(sorted_ids), ptr(perm), ptr(dout), ptr(dweight), int(dweight.dtype == torch.float32),
+         ids.numel(), dweight.shape[1], vocab_start, vocab_end)
 
 
 # ----------------------------------------------------------------------------------------------------------- sequence parallel

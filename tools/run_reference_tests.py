@@ -90,7 +90,10 @@ with tempfile.TemporaryDirectory(prefix="reftests_") as tmp:
                 f.write_text(src.replace(SKIP_EXPR, f"world_size > max(torch.cuda.device_count(), {a.fake_devices})"))
     select = a.select
     if a.suite == "gpu" and not have_determined:
-        select = f"({select}) and not determined" if select else "not determined"
+        # cases that drive the Determined SDK itself (by name; test_train_with_deterministic_behaviour passes
+        # use_determined=True)
+        no_det = "not determined and not deterministic_behaviour"
+        select = f"({select}) and {no_det}" if select else no_det
     env = dict(os.environ, PYTHONPATH=str(REPO))
     cmd = [sys.executable, "-m", "pytest", *targets, "-q", "-p", "no:cacheprovider", "--continue-on-collection-errors",
            "-rfE", "--timeout", str(a.timeout)]
