@@ -256,8 +256,16 @@ class Optimizer(BaseOptimizer):
 
     # ---- checkpoint -------------------------------------------------------------------------------------
     def state_dict(self) -> Dict[str, Any]:
+        """Same keys as the reference (optimizer.py:297-307).  ``optimizer`` has the shape of a torch optimizer's state dict
+        over the flat fp32 partitions — one entry per parameter group, as in the reference where every group is one
+        flattened fp32 tensor: the moments are this rank's arena shards themselves (views, not copies)."""
+        groups = self._torch_style_groups()
+        state = {}
+        for i, (g, tg) in enumerate(zip(self.parameter_groups, groups)):
+            tg["params"] = [i]
+            state[i] = {"step": torch.tensor(float(self.step_index)), "exp_avg": g.exp_avg, "exp_avg_sq": g.exp_avg_sq}
         return {"step_index": self.step_index, "parameter_groups": [g.state_dict() for g in self.parameter_groups],
-                "loss_scaler": self.loss_scaler.state_dict()}
+                "optimizer": {"state": state, "param_groups": groups}, "loss_scaler": self.loss_scaler.state_dict()}
 
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
         self.step_index = sd["step_index"]

@@ -146,6 +146,29 @@ class CudaRNGStateTracker:
 # --------------------------------------------------------------------------------------------------------------
 # topology
 # --------------------------------------------------------------------------------------------------------------
+_exit_hook_installed = False
+
+
+def _destroy_gloo_group_at_exit() -> None:
+    """A script that ends without ``destroy_process_group()`` leaves gloo's worker threads to the interpreter's
+    teardown, which sporadically aborts ("terminate called without an active exception") and turns a finished rank
+    into a failed one.  gloo's destroy is local (no peer has to answer), so it is safe to run it from an exit hook."""
+    global _exit_hook_installed
+    if _exit_hook_installed:
+        return
+    _exit_hook_installed = True
+    import atexit
+
+    def _shutdown() -> None:
+        try:
+            if dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:  # noqa: BLE001  (shutting down anyway)
+            pass
+
+    atexit.register(_shutdown)
+
+
 class Topology:
     def __init__(self, config: TopologyConfig):
         self.config = config
@@ -194,6 +217,8 @@ class Topology:
                 timeout=datetime.timedelta(minutes=torch_distributed_timeout_minutes),
                 **kwargs,
             )
+            if self.backend == "gloo":
+                _destroy_gloo_group_at_exit()
         # every rank creates every group in the same order (collective-consistent)
         for ranks in self.all_pipe_parallel_groups():
             g = dist.new_group(ranks)
