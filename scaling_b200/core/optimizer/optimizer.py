@@ -121,7 +121,7 @@ class Optimizer(BaseOptimizer):
             g.initialize(topology=topology, zero=config.zero, grad_dtype=main_grad_dtype)
         self.loss_scaler = LossScaler(config.loss_scaler, parameter_groups)
         self.step_index = 0
-        dev = topology.device
+        dev = parameter_groups[0].param_arena.device if parameter_groups else topology.device
         self._norm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
         self._nonfinite = torch.zeros(1, dtype=torch.int32, device=dev)
 

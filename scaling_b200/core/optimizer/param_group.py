@@ -110,6 +110,11 @@ class OptimizerParamGroup:
             self._named = [("dummy_parameter", dummy, meta)]
         dtypes = {p.dtype for _, p, _ in self._named}
         assert len(dtypes) == 1, f"all parameters of a group must share a dtype, got {dtypes}"
+        # the arenas live where the parameters live (a model kept on the host is optimised on the host, as with the
+        # reference's torch optimizer); the topology's device is only the default for the empty group
+        devices = {p.device for _, p, _ in self._named}
+        assert len(devices) == 1, f"all parameters of a group must share a device, got {devices}"
+        device = devices.pop()
         self.model_dtype = dtypes.pop()
         self.grad_dtype = grad_dtype or self.model_dtype
         mp_rank = topology.model_parallel_rank

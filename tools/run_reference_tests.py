@@ -70,6 +70,7 @@ p.add_argument("--fake-devices", type=int, default=0,
 p.add_argument("--select", default=None, help="pytest -k expression")
 p.add_argument("--targets", nargs="*", default=None, help="override the file list of the suite")
 p.add_argument("--timeout", type=int, default=900, help="per-test timeout (pytest-timeout)")
+p.add_argument("--tb", default="auto", help="pytest --tb style")
 p.add_argument("--out", default=None)
 a = p.parse_args()
 targets = a.targets or (TARGETS if a.suite == "cpu" else GPU_TARGETS)
@@ -96,7 +97,7 @@ with tempfile.TemporaryDirectory(prefix="reftests_") as tmp:
         select = f"({select}) and {no_det}" if select else no_det
     env = dict(os.environ, PYTHONPATH=str(REPO))
     cmd = [sys.executable, "-m", "pytest", *targets, "-q", "-p", "no:cacheprovider", "--continue-on-collection-errors",
-           "-rfE", "--timeout", str(a.timeout)]
+           "-rfE", "--timeout", str(a.timeout), f"--tb={a.tb}"]
     if select:
         cmd += ["-k", select]
     r = subprocess.run(cmd, cwd=tmp, env=env, capture_output=True, text=True)
