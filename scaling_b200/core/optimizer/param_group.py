@@ -100,9 +100,9 @@ class OptimizerParamGroup:
     def initialize(self, topology: Topology, zero: bool, grad_dtype: Optional[torch.dtype] = torch.float32) -> None:
         self.topology = topology
         self.zero = zero and topology.config.data_parallel_size > 1
-        device = topology.device
         if self.is_dummy:
             # keeps every rank issuing the same collectives when this group is empty here (reference :118-134)
+            device = topology.device
             dummy = torch.nn.Parameter(torch.zeros(1, dtype=torch.bfloat16 if device.type == "cuda" else torch.float32,
                                                    device=device))
             meta = CoreParameterMeta.register_on_parameter(dummy, is_model_parallel=False, layer_index=-1,
