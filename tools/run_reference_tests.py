@@ -67,6 +67,9 @@ p.add_argument("--suite", choices=["cpu", "gpu"], default="cpu",
                help="cpu: the CPU-capable unit files; gpu: the training / transformer acceptance suites")
 p.add_argument("--fake-devices", type=int, default=0,
                help="gpu suite on a box without GPUs (gloo dry run): pretend this many devices in the tests' skip check")
+p.add_argument("--cpu-shim", action="store_true",
+               help="dry run only: a scratch sitecustomize makes Tensor.cuda()/Module.cuda() no-ops and torch.cuda.manual_seed "
+                    "the CPU seed, so unit files that hard-code .cuda() exercise the gloo / CPU path")
 p.add_argument("--select", default=None, help="pytest -k expression")
 p.add_argument("--targets", nargs="*", default=None, help="override the file list of the suite")
 p.add_argument("--timeout", type=int, default=900, help="per-test timeout (pytest-timeout)")
@@ -89,13 +92,19 @@ with tempfile.TemporaryDirectory(prefix="reftests_") as tmp:
             src = f.read_text()
             if SKIP_EXPR in src:
                 f.write_text(src.replace(SKIP_EXPR, f"world_size > max(torch.cuda.device_count(), {a.fake_devices})"))
+    if a.cpu_shim:
+        (Path(tmp) / "sitecustomize.py").write_text(
+            "import torch\n"
+            "torch.Tensor.cuda = lambda self, *a, **k: self\n"
+            "torch.nn.Module.cuda = lambda self, *a, **k: self\n"
+            "torch.cuda.manual_seed = lambda s: torch.manual_seed(s)\n")
     select = a.select
     if a.suite == "gpu" and not have_determined:
         # cases that drive the Determined SDK itself (by name; test_train_with_deterministic_behaviour passes
         # use_determined=True)
         no_det = "not determined and not deterministic_behaviour"
         select = f"({select}) and {no_det}" if select else no_det
-    env = dict(os.environ, PYTHONPATH=str(REPO))
+    env = dict(os.environ, PYTHONPATH=f"{tmp}{os.pathsep}{REPO}" if a.cpu_shim else str(REPO))
     cmd = [sys.executable, "-m", "pytest", *targets, "-q", "-p", "no:cacheprovider", "--continue-on-collection-errors",
            "-rfE", "--timeout", str(a.timeout), f"--tb={a.tb}"]
     if select:
@@ -105,7 +114,7 @@ tail = r.stdout.strip().splitlines()
 summary = tail[-1] if tail else ""
 counts = {k: int(v) for v, k in re.findall(r"(\d+) (passed|failed|skipped|deselected|errors?|warnings?)", summary)}
 not_passing = sorted({ln.split(" - ")[0] for ln in tail if ln.startswith(("FAILED ", "ERROR "))})
-json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices,
+json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices, "cpu_shim": a.cpu_shim,
            "cuda_devices": __import__("torch").cuda.device_count(), "summary": summary, "counts": counts,
            "not_passing": not_passing,
            "note": "collection errors are test files that import private helpers of the reference's implementation "
