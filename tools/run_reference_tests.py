@@ -70,6 +70,9 @@ p.add_argument("--fake-devices", type=int, default=0,
 p.add_argument("--cpu-shim", action="store_true",
                help="dry run only: a scratch sitecustomize makes Tensor.cuda()/Module.cuda() no-ops and torch.cuda.manual_seed "
                     "the CPU seed, so unit files that hard-code .cuda() exercise the gloo / CPU path")
+p.add_argument("--surrogate-tokenizer", action="store_true",
+               help="the checkout lacks tests/transformer/files/alpha-001-128k.json (a large blob); stage the llama2 "
+                    "tokenizer file it does ship under that name so that the tests which only need SOME tokenizer can run")
 p.add_argument("--select", default=None, help="pytest -k expression")
 p.add_argument("--targets", nargs="*", default=None, help="override the file list of the suite")
 p.add_argument("--timeout", type=int, default=900, help="per-test timeout (pytest-timeout)")
@@ -92,6 +95,10 @@ with tempfile.TemporaryDirectory(prefix="reftests_") as tmp:
             src = f.read_text()
             if SKIP_EXPR in src:
                 f.write_text(src.replace(SKIP_EXPR, f"world_size > max(torch.cuda.device_count(), {a.fake_devices})"))
+    if a.surrogate_tokenizer:
+        files = Path(tmp) / "tests" / "transformer" / "files"
+        if not (files / "alpha-001-128k.json").exists() and (files / "llama2-tokenizer.json").exists():
+            shutil.copy(files / "llama2-tokenizer.json", files / "alpha-001-128k.json")
     if a.cpu_shim:
         (Path(tmp) / "sitecustomize.py").write_text(
             "import torch\n"
@@ -114,7 +121,7 @@ tail = r.stdout.strip().splitlines()
 summary = tail[-1] if tail else ""
 counts = {k: int(v) for v, k in re.findall(r"(\d+) (passed|failed|skipped|deselected|errors?|warnings?)", summary)}
 not_passing = sorted({ln.split(" - ")[0] for ln in tail if ln.startswith(("FAILED ", "ERROR "))})
-json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices, "cpu_shim": a.cpu_shim,
+json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices, "cpu_shim": a.cpu_shim, "surrogate_tokenizer": a.surrogate_tokenizer,
            "cuda_devices": __import__("torch").cuda.device_count(), "summary": summary, "counts": counts,
            "not_passing": not_passing,
            "note": "collection errors are test files that import private helpers of the reference's implementation "
