@@ -190,6 +190,24 @@ class FileHandle:
             pass
 
 
+def retry_array_from_file(file_handle: FileHandle, dtype: Any, count: int, offset: int, max_attempts: int = 5,
+                          max_delay: int = 32) -> np.ndarray:
+    """``count`` items of ``dtype`` at BYTE ``offset`` of the file behind ``file_handle``, re-opened and retried when the
+    read comes back empty (``np.fromfile`` does not look at errno: a stale network-filesystem handle shows as a
+    zero-length result) — reference file_dataset.py:151-199.  A short but non-empty read is an error, not a retry."""
+
+    def op(f: IO[Any]) -> np.ndarray:
+        res = np.fromfile(f, dtype=dtype, count=count, offset=offset)
+        f.seek(0)  # fromfile leaves the position behind the data; the handle is reused with absolute offsets
+        if len(res) == 0 and count != 0:
+            raise RetryableException(f"expected {count} items of {dtype} at offset {offset} of {file_handle._path}, got none")
+        if len(res) != count:
+            raise Exception(f"expected {count} items of {dtype} at offset {offset} of {file_handle._path}, got {len(res)}")
+        return res
+
+    return file_handle.retry_operation(op, max_attempts=max_attempts, max_delay=max_delay)
+
+
 class FileDataset(_PrefixFiles):
     """Same format as :class:`MemoryMapDataset`, read with explicit file IO and retries."""
 
@@ -205,14 +223,7 @@ class FileDataset(_PrefixFiles):
 
     @staticmethod
     def _read(handle: FileHandle, dtype: np.dtype, count: int, offset_items: int) -> np.ndarray:
-        def op(f: IO[Any]) -> np.ndarray:
-            f.seek(offset_items * dtype.itemsize)
-            arr = np.fromfile(f, dtype=dtype, count=count)
-            if len(arr) != count:
-                raise RetryableException(f"short read: wanted {count} items, got {len(arr)}")
-            return arr
-
-        return handle.retry_operation(op)
+        return retry_array_from_file(handle, dtype, count, offset_items * np.dtype(dtype).itemsize)
 
     def __len__(self) -> int:
         return self.document_count
