@@ -125,20 +125,38 @@ def _first_match(name: str, patterns: Sequence[str]) -> Optional[str]:
     return next((p for p in patterns if re.search(p, name) is not None), None)
 
 
+def _find_matching_param(key: NamedParameterMeta, data: Sequence[str]) -> Optional[str]:
+    """First pattern of ``data`` that matches the parameter's name (reference model.py:385-386)."""
+    return _first_match(key[0], data)
+
+
+def _filter_by_param(parameters_exclude: Sequence[str], parameter_list: List[NamedParameterMeta]) -> List[NamedParameterMeta]:
+    return [p for p in parameter_list if _find_matching_param(p, parameters_exclude) is None]
+
+
+def _find_global_unmatched_parameters(found: Set[str], finetunable_parameters: Sequence[str]) -> Set[str]:
+    """Patterns that matched no parameter on ANY rank (a pipeline stage only sees its own layers)."""
+    missing = set(finetunable_parameters) - found
+    if dist.is_available() and dist.is_initialized():
+        gathered: List[Any] = [None] * dist.get_world_size()
+        dist.all_gather_object(gathered, missing)
+        missing = set.intersection(*gathered)
+    return missing
+
+
 def _extract_parameters(training: TrainingConfig, named: List[NamedParameterMeta]):
     """Split into (embedding group, no-weight-decay group, weight-decay group) — `.bias` suffix ⇒ no decay (so bitfit
-    biases `bias_<n>` do get decay, like the reference model.py:343-345); finetuning keeps only matching names."""
+    biases `bias_<n>` do get decay, like the reference model.py:343-345); finetuning keeps only matching names and a
+    pattern that matches nothing on any rank is an error (reference model.py:329-364)."""
     wd, no_wd, emb = [], [], []
     found: Set[str] = set()
     for item in named:
         name = item[0]
         if training.finetune:
-            m = _first_match(name, training.finetunable_parameters)
+            m = _find_matching_param(item, training.finetunable_parameters)
             if m is None:
                 continue
             found.add(m)
-        if training.parameters_exclude and _first_match(name, training.parameters_exclude) is not None:
-            continue
         if name.endswith(".bias"):
             no_wd.append(item)
         elif training.use_separate_lr_on_embeddings and name == "embedding.weight":
@@ -146,7 +164,15 @@ def _extract_parameters(training: TrainingConfig, named: List[NamedParameterMeta
             emb.append(item)
         else:
             wd.append(item)
-    return emb, no_wd, wd, found
+    if training.finetune:
+        missing = _find_global_unmatched_parameters(found, training.finetunable_parameters)
+        if missing:
+            raise ValueError(f"Unmatched finetunable parameters: {missing}")
+    if training.parameters_exclude:
+        wd = _filter_by_param(training.parameters_exclude, wd)
+        no_wd = _filter_by_param(training.parameters_exclude, no_wd)
+        emb = _filter_by_param(training.parameters_exclude, emb)
+    return emb, no_wd, wd
 
 
 def get_parameter_groups(context: TransformerContext, model: TransformerParallelModule,
@@ -156,20 +182,12 @@ def get_parameter_groups(context: TransformerContext, model: TransformerParallel
     lr = learning_rate_scheduler_config or cfg.learning_rate_scheduler
     emb_lr = embedding_learning_rate_scheduler_config or cfg.embedding_learning_rate_scheduler
     named = model.named_parameters_with_meta()
-    emb, no_wd, wd, found = _extract_parameters(cfg.training, named)
+    emb, no_wd, wd = _extract_parameters(cfg.training, named)
     topo = context.topology
     distributed = topo.is_distributed_initialized
     counts = torch.tensor([len(wd), len(no_wd), len(emb)], dtype=torch.long, device=topo.device)
     if distributed:
         dist.all_reduce(counts, op=dist.ReduceOp.MAX)  # a group must exist everywhere if it exists anywhere
-    if cfg.training.finetune:
-        missing = set(cfg.training.finetunable_parameters) - found
-        if distributed:
-            gathered: List[Any] = [None] * dist.get_world_size()
-            dist.all_gather_object(gathered, missing)
-            missing = set.intersection(*gathered)
-        if missing:
-            raise ValueError(f"Unmatched finetunable parameters: {missing}")
     assert int(counts.sum()) > 0, "did not specify any finetuneable parameters on any rank"
     logger.info(f"training parameters: {sorted({n for n, _, _ in wd + no_wd + emb})}")
     # true freezing: parameters outside every group neither compute nor keep gradients
