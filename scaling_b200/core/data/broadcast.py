@@ -15,24 +15,49 @@ from ..topology import Topology
 MAX_DIMS = 8
 
 
-def sync_sizes(tensors: Optional[List[Optional[torch.Tensor]]], n: int, topology: Topology) -> List[Optional[List[int]]]:
-    """Broadcast the shapes (or "is None") of ``n`` tensors; -1 padding marks unused dims, -2 a missing tensor."""
-    sizes = torch.full((n, MAX_DIMS), -1, dtype=torch.long)
-    if topology.model_parallel_rank == 0:
-        assert tensors is not None and len(tensors) == n
+_MAX_DATA_DIM = MAX_DIMS
+
+
+def _build_tensor_sizes(tensors: List[Optional[torch.Tensor]], model_parallel_rank: int) -> List[int]:
+    """Shape table as one flat int list, ``MAX_DIMS`` entries per tensor: the sizes, padded with -1 (reference
+    broadcast_data.py:20-41).  Only TP rank 0 knows the shapes; the others send all -1.  Extension: -2 in the first entry
+    marks a tensor that is None."""
+    sizes = [-1] * (len(tensors) * _MAX_DATA_DIM)
+    if model_parallel_rank == 0:
         for i, t in enumerate(tensors):
             if t is None:
-                sizes[i, 0] = -2
-            else:
-                assert t.dim() <= MAX_DIMS
-                for d, s in enumerate(t.shape):
-                    sizes[i, d] = s
-    sizes = sizes.to(topology.device)
+                sizes[i * _MAX_DATA_DIM] = -2
+                continue
+            assert t.dim() <= _MAX_DATA_DIM, f"tensors with more than {_MAX_DATA_DIM} dimensions cannot be broadcast"
+            for d, n in enumerate(t.shape):
+                sizes[i * _MAX_DATA_DIM + d] = int(n)
+    return sizes
+
+
+def _unpack_sizes(flat: List[int]) -> tuple:
+    """(shapes, element counts) from a table built by :func:`_build_tensor_sizes`."""
+    shapes: List[List[int]] = []
+    numels: List[int] = []
+    for i in range(0, len(flat), _MAX_DATA_DIM):
+        shape = [int(n) for n in flat[i:i + _MAX_DATA_DIM] if n >= 0]
+        shapes.append(shape)
+        k = 1
+        for n in shape:
+            k *= n
+        numels.append(k)
+    return shapes, numels
+
+
+def sync_sizes(tensors: Optional[List[Optional[torch.Tensor]]], n: int, topology: Topology) -> List[Optional[List[int]]]:
+    """Broadcast the shapes (or "is None") of ``n`` tensors; -1 padding marks unused dims, -2 a missing tensor."""
+    if topology.model_parallel_rank == 0:
+        assert tensors is not None and len(tensors) == n
+    table = _build_tensor_sizes(tensors if topology.model_parallel_rank == 0 else [None] * n, topology.model_parallel_rank)
+    sizes = torch.tensor(table, dtype=torch.long).to(topology.device)
     dist.broadcast(sizes, src=topology.model_parallel_ranks[0], group=topology.model_parallel_group)
-    out: List[Optional[List[int]]] = []
-    for row in sizes.cpu().tolist():
-        out.append(None if row[0] == -2 else [s for s in row if s >= 0])
-    return out
+    flat = sizes.cpu().tolist()
+    shapes, _ = _unpack_sizes(flat)
+    return [None if flat[i * _MAX_DATA_DIM] == -2 else shape for i, shape in enumerate(shapes)]
 
 
 def broadcast_data(tensors: Optional[List[Optional[torch.Tensor]]], dtype: torch.dtype, topology: Topology,

@@ -48,6 +48,11 @@ def is_date(text: str) -> bool:
         return False
 
 
+def _check_if_in_rank(target_rank: Optional[int], ranks: Optional[List[int]]) -> bool:
+    """Name of this predicate in the reference (logger_config.py:106-111)."""
+    return _rank_allowed(target_rank, ranks)
+
+
 def _rank_allowed(rank: Optional[int], ranks: Optional[List[int]]) -> bool:
     if rank is None:
         return False
