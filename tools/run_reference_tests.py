@@ -124,8 +124,8 @@ not_passing = sorted({ln.split(" - ")[0] for ln in tail if ln.startswith(("FAILE
 json.dump({"suite": a.suite, "targets": targets, "select": select, "fake_devices": a.fake_devices, "cpu_shim": a.cpu_shim, "surrogate_tokenizer": a.surrogate_tokenizer,
            "cuda_devices": __import__("torch").cuda.device_count(), "summary": summary, "counts": counts,
            "not_passing": not_passing,
-           "note": "collection errors are test files that import private helpers of the reference's implementation "
-                   "(names starting with an underscore) which are not part of its API"}, open(out, "w"), indent=1)
+           "note": "not_passing lists every failing or uncollectable case; see profiles/README.md for what each one needs"},
+          open(out, "w"), indent=1)
 print(summary)
 for ln in not_passing:
     print(" ", ln)
