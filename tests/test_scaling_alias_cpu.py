@@ -83,3 +83,26 @@ def test_blended_dataset_loop_shim_writes_the_wheel_files(tmp_path):
     idx = np.fromfile(stem + ".bin", dtype=np.dtype(meta["dtype"])).reshape(meta["shape"])
     assert idx.shape == (8, 2) and sorted(idx[idx[:, 0] == 1][:, 1].tolist()) == [0, 1, 2, 3, 4]
     assert Path(stem + ".input.json").is_file()
+
+
+def test_reference_unit_files_run_against_the_alias(tmp_path):
+    """The reference's own test files are the oracle for API parity: a few fast ones (batch-broadcast shape table,
+    finetuning parameter selection, retried file reads) run unchanged through the alias.  Skipped where the reference
+    checkout is not available."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    import pytest
+
+    ref = Path("/root/reference")
+    if not (ref / "tests").is_dir():
+        pytest.skip("reference checkout not present")
+    repo = Path(__file__).resolve().parents[1]
+    out = tmp_path / "ref.json"
+    subprocess.run([sys.executable, str(repo / "tools" / "run_reference_tests.py"), "--reference", str(ref), "--out", str(out),
+                    "--targets", "tests/core/test_data/test_broadcast_data.py", "tests/core/test_data/test_file_dataset.py",
+                    "tests/transformer/test_finetuning_parameter.py"], check=True, capture_output=True, timeout=600)
+    res = json.loads(out.read_text())
+    assert res["not_passing"] == [] and res["counts"].get("passed", 0) >= 30, res
